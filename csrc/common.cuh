@@ -1,0 +1,167 @@
+// Shared device/host helpers for liberasurehead (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../include/erasurehead.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "liberasurehead targets sm_100a (Blackwell) only"
+#endif
+
+namespace eh {
+
+// ---------------------------------------------------------------- host error plumbing
+void set_error(const char* fmt, ...);
+#define EH_CUDA(call)                                                                        \
+    do {                                                                                     \
+        cudaError_t e__ = (call);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            eh::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return (int)e__;                                                                 \
+        }                                                                                    \
+    } while (0)
+#define EH_REQUIRE(cond, ...)                                                                \
+    do {                                                                                     \
+        if (!(cond)) {                                                                       \
+            eh::set_error(__VA_ARGS__);                                                      \
+            return EH_EINVAL;                                                                \
+        }                                                                                    \
+    } while (0)
+
+struct DevInfo {
+    int device = -1;
+    int sm_count = 0;
+    int coop = 0;
+};
+const DevInfo& dev_info();
+// Process-wide launch sequence number for the decision word of the cooperative gradient kernels.
+uint32_t next_launch_seq();
+
+// ---------------------------------------------------------------- workspace control block
+// Lives at lay.off_ctl in every GPU's workspace.  128-byte separated words.
+struct alignas(128) CtlWord {
+    uint32_t v;
+    uint32_t pad[31];
+};
+enum CtlIndex {
+    CTL_BETA_FLAG = 0,   // round+1 once beta of that round is readable in beta[round&1]
+    CTL_ERROR     = 1,   // sticky error code (watchdogs)
+    CTL_DECISION  = 2,   // worker kernel: (stamp<<1 | stale) decision broadcast by CTA 0
+    CTL_COUNT     = 8,
+};
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- device primitives
+__device__ __forceinline__ uint64_t globaltimer() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t atom_add_acq_rel_gpu(uint32_t* p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void nanosleep(uint32_t ns) {
+    asm volatile("nanosleep.u32 %0;" ::"r"(ns));
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Device-wide barrier for co-resident grids (cooperative launch).  `counter` is a monotonically
+// increasing ticket word; `generation` counts barriers already passed by this CTA.
+// Every thread of the CTA must call it.  Data written before is visible after (gpu scope).
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t& generation) {
+    __syncthreads();
+    generation += 1;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atom_add_acq_rel_gpu(counter, 1u);
+        const uint32_t target = generation * gridDim.x;
+        while (ld_acquire_gpu(counter) < target) nanosleep(32);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// ---- mbarrier / TMA bulk copy (sm_90+ PTX; SASS: SYNCS / UBLKCP)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+// 1-D TMA bulk copy global -> shared, completion on an mbarrier (bytes % 16 == 0).
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes,
+                                            uint64_t* bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+        "[%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(smem_dst)),
+        "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+#endif  // __CUDACC__
+
+}  // namespace eh

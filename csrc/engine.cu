@@ -1,0 +1,63 @@
+// Native round loop (see eh_run_rounds in erasurehead.h).
+//
+// The host only *enqueues*: all cross-GPU ordering is carried by the stamped flags in the
+// peer-mapped workspaces (worker kernels spin on the parameter flag, the decoder kernel spins on
+// arrival flags), so `n_rounds` rounds are in flight on every GPU's stream with no host
+// synchronisation -- the device-side analogue of the reference's pre-posted Irecv lists
+// (approximate_coding.py:102-114) without their buffer-aliasing races.
+#include "workspace.cuh"
+
+extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_rounds, int r0, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(plan && plan->d_ws_local && plan->d_ws_root && plan->d_scratch, "run_rounds: null pointer");
+    EH_REQUIRE(plan->n_jobs == 0 || plan->jobs, "run_rounds: null job array");
+    EH_REQUIRE(first_round >= 0 && n_rounds >= 0, "run_rounds: bad round range");
+    const eh_ws_layout& lay = plan->lay;
+    uint32_t* beta_flag = ws_beta_flag(plan->d_ws_local, lay);
+    uint32_t* err = ws_error(plan->d_ws_local, lay);
+    for (int it = 0; it < n_rounds; ++it) {
+        const int round = first_round + it;
+        const int par = round & 1;
+        const uint32_t stamp = (uint32_t)round + 1u;
+        for (int q = 0; q < plan->n_jobs; ++q) {
+            const eh_worker_job& wj = plan->jobs[q];
+            EH_REQUIRE(wj.worker >= 0 && wj.worker < (int)lay.n_workers && wj.msg >= 0 && wj.msg < (int)lay.n_msgs,
+                       "run_rounds: job %d addresses slot (%d,%d) outside the workspace", q, wj.worker, wj.msg);
+            float* out = ws_slot(plan->d_ws_root, lay, wj.worker, wj.msg, par);
+            uint32_t* flag = ws_flag(plan->d_ws_root, lay, wj.worker, wj.msg);
+            const float* beta = ws_beta(plan->d_ws_local, lay, par);
+            int rc;
+            if (!wj.sparse) {
+                eh_grad_job j;
+                memset(&j, 0, sizeof(j));
+                for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
+                    j.d_X[i] = (const float*)wj.d_X[i];
+                    j.d_y[i] = wj.d_y[i];
+                    j.coeff[i] = wj.coeff[i];
+                }
+                j.d_beta = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
+                j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.ld = wj.ld_or_nnz;
+                j.model = wj.model; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
+                rc = eh_grad_dense(&j, plan->d_scratch, plan->scratch_bytes, stream);
+            } else {
+                eh_grad_ell_job j;
+                memset(&j, 0, sizeof(j));
+                for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
+                    j.d_idx[i] = (const int32_t*)wj.d_X[i];
+                    j.d_y[i] = wj.d_y[i];
+                    j.coeff[i] = wj.coeff[i];
+                }
+                j.d_beta = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
+                j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.nnz = wj.ld_or_nnz;
+                j.model = wj.model; j.bias_col = wj.bias_col; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
+                rc = eh_grad_ell(&j, plan->d_scratch, plan->scratch_bytes, stream);
+            }
+            if (rc) return rc;
+        }
+        if (plan->decoder) {
+            int rc = eh_decoder_round(plan->decoder, round, r0 + it, stream);
+            if (rc) return rc;
+        }
+    }
+    return EH_OK;
+}

@@ -1,0 +1,376 @@
+// Fused one-pass encoded gradient for dense fp32 features (ops K1 + K2' + K3 of SURVEY 2.4).
+//
+//   g = sum_r  X[r,:] * coeff[seg(r)] * resid(X[r,:].beta, y[r])
+//
+// Reference math: naive.py:137-139 (logistic), naive.py:345-346 (linear), encode folded into the
+// residual numerator as in coded.py:92-95,184.  The reference does two BLAS GEMVs (X read
+// twice, float64, CPU).  Here X is read from HBM exactly once:
+//
+//   * a producer warp streams RB-row tiles with 1-D TMA bulk copies (cp.async.bulk -> UBLKCP)
+//     into a shared-memory ring guarded by full/empty mbarriers, L2 evict-first;
+//   * 8 consumer warps pull their 4*DV columns of each row into registers, form the row dots
+//     (warp shuffle + one named barrier per tile), evaluate the residual and do the rank-1
+//     accumulate from the same registers;
+//   * per-CTA partial gradients meet in `scratch`, a device-wide barrier (cooperative launch)
+//     lets 32-column-group reducers sum them in a fixed order (deterministic), and the result is
+//     stored straight into the destination slot -- local or a peer GPU's NVLink-mapped memory --
+//     followed by a release/system flag (the "ship" of the message, replacing MPI Isend,
+//     naive.py:150).
+//
+// The kernel starts prefetching X while it still waits for this round's parameters
+// (`d_beta_flag`), i.e. the parameter broadcast overlaps the first tiles of the next round.
+#include "common.cuh"
+
+namespace eh {
+
+constexpr int GD_CONSUMER_WARPS = 8;
+constexpr int GD_CONSUMERS = GD_CONSUMER_WARPS * 32;
+constexpr int GD_THREADS = GD_CONSUMERS + 32;
+constexpr int GD_MAX_STAGES = 8;
+constexpr int GD_MAX_SEGS = EH_MAX_SEGS;
+constexpr int GD_SMEM_BUDGET = 220 * 1024;
+
+struct GradScratchHdr {          // first 512 bytes of the scratch buffer
+    alignas(128) uint32_t barrier;     // device-wide barrier ticket
+    alignas(128) uint32_t done;        // final ticket
+    alignas(128) uint32_t decision;    // (seq << 2) | code, written by CTA 0
+    alignas(128) uint32_t pad;
+};
+constexpr uint32_t DEC_GO = 1, DEC_SKIP = 2;
+
+struct GradParams {
+    const float* seg_X[EH_MAX_SEGS];
+    const float* seg_y[EH_MAX_SEGS];
+    const float* beta;
+    float* out;
+    uint32_t* flag;
+    const uint32_t* beta_flag;
+    uint32_t* err;
+    GradScratchHdr* hdr;
+    float* partials;             // [grid][ldp]
+    int d, ld, ldp;
+    int rows_per_seg, n_segs, model;
+    int n_stages;
+    int steps_per_seg;
+    long long n_steps;
+    uint32_t stamp, seq;
+    unsigned long long timeout_ns;
+    float coeff[GD_MAX_SEGS];
+};
+
+__device__ __forceinline__ float residual(int model, float p, float y) {
+    if (model == EH_MODEL_LOGISTIC) {
+        // -y / (exp(p*y) + 1); exp overflow -> inf -> -0, matching the float64 limit
+        return __fdividef(-y, __expf(p * y) + 1.0f);
+    }
+    return -2.0f * (y - p);
+}
+
+template <int DV, int RB>
+__global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int G = gridDim.x, b = blockIdx.x;
+    const uint32_t stage_bytes = (uint32_t)RB * p.ld * 4u;
+    float* stages = reinterpret_cast<float*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)p.n_stages * stage_bytes);
+    uint64_t* empty = full + GD_MAX_STAGES;
+    float* red = reinterpret_cast<float*>(empty + GD_MAX_STAGES);      // [2][8][RB]
+    __shared__ uint32_t s_decision;
+
+    const long long my_steps = (b < p.n_steps) ? (p.n_steps - b + G - 1) / G : 0;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.n_stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], GD_CONSUMER_WARPS);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    // ---------------- decision: wait for beta of this round (CTA 0 decides for the grid)
+    uint32_t code = DEC_GO;
+    if (warp == GD_CONSUMER_WARPS) {
+        // producer warp: prefetch the first tiles while the parameters are still in flight
+        long long issued = 0;
+        uint64_t pol = l2_policy_evict_first();
+        if (lane == 0) {
+            const long long pre = my_steps < p.n_stages ? my_steps : p.n_stages;
+            for (; issued < pre; ++issued) {
+                const long long step = b + issued * G;
+                const int sg = (int)(step / p.steps_per_seg);
+                const int row0 = (int)(step % p.steps_per_seg) * RB;
+                const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
+                const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
+                const int st = (int)(issued % p.n_stages);
+                mbar_arrive_expect_tx(&full[st], bytes);
+                tma_load_1d(stages + (size_t)st * RB * p.ld, p.seg_X[sg] + (size_t)row0 * p.ld, bytes, &full[st], pol);
+            }
+        }
+        if (b == 0 && lane == 0) {
+            code = DEC_GO;
+            if (p.beta_flag) {
+                const uint64_t t0 = globaltimer();
+                while (true) {
+                    const uint32_t f = ld_acquire_sys(p.beta_flag);
+                    if (f == p.stamp) break;
+                    if (f > p.stamp) { code = DEC_SKIP; break; }                  // round already over
+                    if (p.err && ld_acquire_sys(p.err) != 0) { code = DEC_SKIP; break; }
+                    if (globaltimer() - t0 > p.timeout_ns) {
+                        if (p.err) atomicCAS(p.err, 0u, (uint32_t)(-EH_ETIMEOUT));
+                        code = DEC_SKIP;
+                        break;
+                    }
+                    nanosleep(64);
+                }
+            }
+            st_release_gpu(&p.hdr->decision, (p.seq << 2) | code);
+        }
+        if (lane == 0) {
+            if (b != 0) {
+                uint32_t v;
+                while (((v = ld_acquire_gpu(&p.hdr->decision)) >> 2) != p.seq) nanosleep(32);
+                code = v & 3u;
+            }
+            s_decision = code;
+        }
+        __syncwarp();
+        code = __shfl_sync(0xffffffffu, code, 0);
+        // named barrier 1: hand the decision to the consumers
+        asm volatile("bar.sync 1, %0;" ::"r"(GD_THREADS) : "memory");
+        if (code == DEC_SKIP) {
+            if (lane == 0)
+                for (long long k = 0; k < issued; ++k) mbar_wait(&full[(int)(k % p.n_stages)], 0);
+            return;
+        }
+        // ---------------- producer main loop
+        if (lane == 0) {
+            for (long long k = issued; k < my_steps; ++k) {
+                const int st = (int)(k % p.n_stages);
+                const uint32_t use = (uint32_t)(k / p.n_stages);      // >= 1 here
+                mbar_wait(&empty[st], (use - 1) & 1);
+                const long long step = b + k * G;
+                const int sg = (int)(step / p.steps_per_seg);
+                const int row0 = (int)(step % p.steps_per_seg) * RB;
+                const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
+                const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
+                mbar_arrive_expect_tx(&full[st], bytes);
+                tma_load_1d(stages + (size_t)st * RB * p.ld, p.seg_X[sg] + (size_t)row0 * p.ld, bytes, &full[st], pol);
+            }
+        }
+        __syncwarp();
+    } else {
+        asm volatile("bar.sync 1, %0;" ::"r"(GD_THREADS) : "memory");
+        code = s_decision;
+        if (code == DEC_SKIP) return;
+
+        // ---------------- consumers
+        const int ld4 = p.ld >> 2;
+        float4 bt[DV], acc[DV];
+#pragma unroll
+        for (int v = 0; v < DV; ++v) {
+            const int c4 = v * GD_CONSUMERS + tid;
+            acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int c = c4 * 4;
+            if (c + 0 < p.d) t.x = p.beta[c + 0];
+            if (c + 1 < p.d) t.y = p.beta[c + 1];
+            if (c + 2 < p.d) t.z = p.beta[c + 2];
+            if (c + 3 < p.d) t.w = p.beta[c + 3];
+            bt[v] = t;
+        }
+        for (long long k = 0; k < my_steps; ++k) {
+            const int st = (int)(k % p.n_stages);
+            const uint32_t use = (uint32_t)(k / p.n_stages);
+            const long long step = b + k * G;
+            const int sg = (int)(step / p.steps_per_seg);
+            const int row0 = (int)(step % p.steps_per_seg) * RB;
+            const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
+            // labels / encode weight of this tile (independent of the TMA data)
+            const float cf = p.coeff[sg];
+            const float* ys = p.seg_y[sg] + row0;
+            float yv[RB];
+#pragma unroll
+            for (int r = 0; r < RB; ++r) yv[r] = (r < nr) ? __ldg(ys + r) : 0.f;
+            mbar_wait(&full[st], use & 1);
+            const float4* tile = reinterpret_cast<const float4*>(stages + (size_t)st * RB * p.ld);
+            float4 x[RB][DV];
+            float dot[RB];
+#pragma unroll
+            for (int r = 0; r < RB; ++r) {
+                dot[r] = 0.f;
+#pragma unroll
+                for (int v = 0; v < DV; ++v) {
+                    const int c4 = v * GD_CONSUMERS + tid;
+                    x[r][v] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (r < nr && c4 < ld4) x[r][v] = tile[(size_t)r * ld4 + c4];
+                    dot[r] = fmaf(x[r][v].x, bt[v].x, dot[r]);
+                    dot[r] = fmaf(x[r][v].y, bt[v].y, dot[r]);
+                    dot[r] = fmaf(x[r][v].z, bt[v].z, dot[r]);
+                    dot[r] = fmaf(x[r][v].w, bt[v].w, dot[r]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < RB; ++r) dot[r] = warp_sum(dot[r]);
+            // all lanes' tile reads are complete (their values fed the shuffles): free the slot
+            float* redw = red + ((k & 1) * GD_CONSUMER_WARPS + warp) * RB;
+            if (lane == 0) {
+#pragma unroll
+                for (int r = 0; r < RB; ++r) redw[r] = dot[r];
+                mbar_arrive(&empty[st]);
+            }
+            asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
+            const float* redk = red + (k & 1) * GD_CONSUMER_WARPS * RB;
+#pragma unroll
+            for (int r = 0; r < RB; ++r) {
+                if (r < nr) {
+                    float pr = 0.f;
+#pragma unroll
+                    for (int w = 0; w < GD_CONSUMER_WARPS; ++w) pr += redk[w * RB + r];
+                    const float rs = cf * residual(p.model, pr, yv[r]);
+#pragma unroll
+                    for (int v = 0; v < DV; ++v) {
+                        acc[v].x = fmaf(rs, x[r][v].x, acc[v].x);
+                        acc[v].y = fmaf(rs, x[r][v].y, acc[v].y);
+                        acc[v].z = fmaf(rs, x[r][v].z, acc[v].z);
+                        acc[v].w = fmaf(rs, x[r][v].w, acc[v].w);
+                    }
+                }
+            }
+        }
+        // ---------------- per-CTA partial -> scratch
+        float4* mine = reinterpret_cast<float4*>(p.partials + (size_t)b * p.ldp);
+#pragma unroll
+        for (int v = 0; v < DV; ++v) {
+            const int c4 = v * GD_CONSUMERS + tid;
+            if (c4 < ld4) __stcg(mine + c4, acc[v]);
+        }
+    }
+
+    // ---------------- device-wide barrier, then ordered column-group reduction + ship
+    uint32_t gen = 0;
+    grid_barrier(&p.hdr->barrier, gen);
+
+    if (warp < GD_CONSUMER_WARPS) {
+        const int ld4 = p.ld >> 2;
+        const int n_groups = (ld4 + 31) / 32;                 // 32 float4 columns per group
+        float4* sred = reinterpret_cast<float4*>(smem_raw);   // [8][32] float4, ring is idle now
+        for (int grp = b; grp < n_groups; grp += G) {
+            const int c4 = grp * 32 + lane;
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c4 < ld4) {
+                for (int row = warp; row < G; row += GD_CONSUMER_WARPS) {
+                    const float4 t = __ldcg(reinterpret_cast<const float4*>(p.partials + (size_t)row * p.ldp) + c4);
+                    s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+                }
+            }
+            sred[warp * 32 + lane] = s;
+            asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
+            if (warp == 0 && c4 < ld4) {
+                float4 t = sred[lane];
+#pragma unroll
+                for (int w = 1; w < GD_CONSUMER_WARPS; ++w) {
+                    const float4 u = sred[w * 32 + lane];
+                    t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+                }
+                const int c = c4 * 4;
+                if (c + 3 < p.d) {
+                    *reinterpret_cast<float4*>(p.out + c) = t;
+                } else {
+                    if (c + 0 < p.d) p.out[c + 0] = t.x;
+                    if (c + 1 < p.d) p.out[c + 1] = t.y;
+                    if (c + 2 < p.d) p.out[c + 2] = t.z;
+                }
+            }
+            asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence_system();
+        const uint32_t old = atom_add_acq_rel_gpu(&p.hdr->done, 1u);
+        if (old == (uint32_t)G - 1) {
+            // last CTA: every CTA is past the barrier wait -> safe to recycle the counters
+            p.hdr->barrier = 0;
+            p.hdr->done = 0;
+            __threadfence_system();
+            if (p.flag) st_release_sys(p.flag, p.stamp);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ host
+
+template <int DV, int RB>
+static int launch(const eh_grad_job* j, GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
+    const DevInfo& di = dev_info();
+    const size_t stage_bytes = (size_t)RB * p.ld * 4;
+    int stages = (int)((GD_SMEM_BUDGET - 1024) / stage_bytes);
+    if (stages > GD_MAX_STAGES) stages = GD_MAX_STAGES;
+    EH_REQUIRE(stages >= 2, "grad_dense: row tile too large for shared memory (ld=%d)", p.ld);
+    const size_t tail = 2 * GD_MAX_STAGES * sizeof(uint64_t) + 2 * GD_CONSUMER_WARPS * RB * sizeof(float);
+    size_t smem = stages * stage_bytes + tail;
+    if (smem < 8 * 32 * sizeof(float4) + tail) smem = 8 * 32 * sizeof(float4) + tail;
+    p.n_stages = stages;
+    p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
+    p.n_steps = (long long)p.steps_per_seg * p.n_segs;
+    auto kern = grad_dense_kernel<DV, RB>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
+        attr_done = true;
+    }
+    long long grid = di.sm_count;
+    if (grid > p.n_steps) grid = p.n_steps;
+    if (grid < 1) grid = 1;
+    p.ldp = p.ld;
+    const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.ldp * sizeof(float);
+    EH_REQUIRE(scratch_bytes >= need, "grad_dense: scratch too small (%zu < %zu)", scratch_bytes, need);
+    p.hdr = reinterpret_cast<GradScratchHdr*>(d_scratch);
+    p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(d_scratch) + sizeof(GradScratchHdr));
+    void* args[] = {(void*)&p};
+    EH_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream));
+    (void)j;
+    return EH_OK;
+}
+
+}  // namespace eh
+
+extern "C" size_t eh_grad_dense_scratch_bytes(int d) {
+    const int ld = (d + 3) & ~3;
+    int sm = eh::dev_info().sm_count;
+    if (sm <= 0) sm = 160;
+    return sizeof(eh::GradScratchHdr) + (size_t)sm * (size_t)(ld + 32) * sizeof(float);
+}
+
+extern "C" int eh_grad_dense(const eh_grad_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(j && j->d_beta && j->d_out && d_scratch, "grad_dense: null pointer");
+    EH_REQUIRE(j->n_segs > 0 && j->n_segs <= EH_MAX_SEGS, "grad_dense: n_segs=%d out of range (1..%d)", j->n_segs,
+               EH_MAX_SEGS);
+    EH_REQUIRE(j->rows_per_seg > 0 && j->d > 0, "grad_dense: empty problem");
+    EH_REQUIRE(j->ld >= j->d && (j->ld % 4) == 0, "grad_dense: ld (%d) must be >= d and a multiple of 4", j->ld);
+    EH_REQUIRE(j->ld <= 8192, "grad_dense: ld=%d > 8192 not supported by the one-pass kernel", j->ld);
+    GradParams p;
+    memset(&p, 0, sizeof(p));
+    for (int i = 0; i < j->n_segs; ++i) {
+        EH_REQUIRE(j->d_X[i] && j->d_y[i], "grad_dense: null segment %d", i);
+        EH_REQUIRE(((uintptr_t)j->d_X[i] % 16) == 0, "grad_dense: X must be 16-byte aligned");
+        p.seg_X[i] = j->d_X[i];
+        p.seg_y[i] = j->d_y[i];
+        p.coeff[i] = j->coeff[i];
+    }
+    p.beta = j->d_beta; p.out = j->d_out;
+    p.flag = j->d_flag; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
+    p.d = j->d; p.ld = j->ld;
+    p.rows_per_seg = j->rows_per_seg; p.n_segs = j->n_segs; p.model = j->model;
+    p.stamp = j->stamp; p.seq = next_launch_seq();
+    p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (j->ld <= 1024) return launch<1, 8>(j, p, d_scratch, scratch_bytes, st);
+    if (j->ld <= 2048) return launch<2, 4>(j, p, d_scratch, scratch_bytes, st);
+    if (j->ld <= 4096) return launch<4, 4>(j, p, d_scratch, scratch_bytes, st);
+    return launch<8, 2>(j, p, d_scratch, scratch_bytes, st);
+}

@@ -1,0 +1,149 @@
+// Host runtime: error reporting, device info, peer-mapped workspace management (CUDA IPC).
+//
+// The workspace replaces the reference's mpi4py buffers: `msgBuffers[j]` / the pre-posted
+// Irecv targets (naive.py:68-79) become flagged, double-buffered slots in rank 0's memory that
+// every worker GPU stores into directly over NVLink; the per-round `Isend(beta)` loop
+// (naive.py:97-98) becomes peer stores into each GPU's `beta[2][d]` buffer.
+#include <stdarg.h>
+
+#include "workspace.cuh"
+
+namespace eh {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+const DevInfo& dev_info() {
+    static DevInfo cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        static DevInfo none;
+        return none;
+    }
+    DevInfo& di = cache[dev];
+    if (di.device != dev) {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, dev) == cudaSuccess) {
+            di.sm_count = prop.multiProcessorCount;
+            di.coop = prop.cooperativeLaunch;
+            di.device = dev;
+        }
+    }
+    return di;
+}
+
+uint32_t next_launch_seq() {
+    static uint32_t seq = 1;
+    const uint32_t v = seq++;
+    if (seq >= (1u << 30)) seq = 1;
+    return v;
+}
+
+static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+__global__ void ws_error_read_kernel(const uint32_t* err, int* out) { *out = (int)*err; }
+
+}  // namespace eh
+
+extern "C" const char* eh_last_error(void) { return eh::g_err; }
+extern "C" int eh_version(void) { return 100; }
+
+extern "C" int eh_device_info(int* sm_count, int* grad_dense_ctas, int* decoder_ctas) {
+    const eh::DevInfo& di = eh::dev_info();
+    EH_REQUIRE(di.device >= 0, "no CUDA device");
+    if (sm_count) *sm_count = di.sm_count;
+    if (grad_dense_ctas) *grad_dense_ctas = di.sm_count;
+    if (decoder_ctas) *decoder_ctas = di.sm_count;
+    return EH_OK;
+}
+
+extern "C" int eh_ws_layout_make(int n_workers, int n_msgs, int d, eh_ws_layout* out) {
+    using namespace eh;
+    EH_REQUIRE(out, "ws_layout: null out");
+    EH_REQUIRE(n_workers >= 1 && n_workers <= EH_MAX_WORKERS, "ws_layout: n_workers=%d out of range", n_workers);
+    EH_REQUIRE(n_msgs >= 1 && n_msgs <= EH_MAX_MSGS, "ws_layout: n_msgs=%d out of range", n_msgs);
+    EH_REQUIRE(d >= 1, "ws_layout: d must be positive");
+    memset(out, 0, sizeof(*out));
+    const uint32_t d_pad = (uint32_t)align_up((uint64_t)d, 32);      // 128-byte rows
+    out->n_workers = n_workers;
+    out->n_msgs = n_msgs;
+    out->d_pad = d_pad;
+    uint64_t off = 0;
+    out->off_ctl = off;
+    off += sizeof(CtlWord) * CTL_COUNT;
+    out->off_beta = off = align_up(off, 256);
+    off += 2ull * d_pad * sizeof(float);
+    out->off_flags = off = align_up(off, 256);
+    off += (uint64_t)n_workers * EH_MAX_MSGS * 128;
+    out->off_slots = off = align_up(off, 256);
+    off += (uint64_t)n_workers * n_msgs * 2ull * d_pad * sizeof(float);
+    out->bytes = align_up(off, 256);
+    return EH_OK;
+}
+
+extern "C" int eh_ws_create(const eh_ws_layout* lay, void** d_ws, unsigned char ipc_handle[64]) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws, "ws_create: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    void* p = nullptr;
+    EH_CUDA(cudaMalloc(&p, lay->bytes));
+    EH_CUDA(cudaMemset(p, 0, lay->bytes));
+    if (ipc_handle) {
+        cudaIpcMemHandle_t h;
+        cudaError_t e = cudaIpcGetMemHandle(&h, p);
+        if (e != cudaSuccess) {
+            // single-process use does not need the handle; report but keep the allocation
+            memset(ipc_handle, 0, 64);
+            (void)cudaGetLastError();
+        } else {
+            memcpy(ipc_handle, &h, 64);
+        }
+    }
+    *d_ws = p;
+    return EH_OK;
+}
+
+extern "C" int eh_ws_open(const unsigned char ipc_handle[64], void** d_ws_peer) {
+    using namespace eh;
+    EH_REQUIRE(ipc_handle && d_ws_peer, "ws_open: null argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle, 64);
+    EH_CUDA(cudaIpcOpenMemHandle(d_ws_peer, h, cudaIpcMemLazyEnablePeerAccess));
+    return EH_OK;
+}
+
+extern "C" int eh_ws_close(void* d_ws_peer) {
+    if (d_ws_peer) EH_CUDA(cudaIpcCloseMemHandle(d_ws_peer));
+    return EH_OK;
+}
+
+extern "C" int eh_ws_destroy(void* d_ws) {
+    if (d_ws) EH_CUDA(cudaFree(d_ws));
+    return EH_OK;
+}
+
+extern "C" int eh_ws_reset(const eh_ws_layout* lay, void* d_ws, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws, "ws_reset: null argument");
+    // control words + flags; parameter buffers and slots need no clearing (stamps guard them)
+    EH_CUDA(cudaMemsetAsync((char*)d_ws + lay->off_ctl, 0, sizeof(CtlWord) * CTL_COUNT, (cudaStream_t)stream));
+    EH_CUDA(cudaMemsetAsync((char*)d_ws + lay->off_flags, 0, (size_t)lay->n_workers * EH_MAX_MSGS * 128,
+                            (cudaStream_t)stream));
+    return EH_OK;
+}
+
+extern "C" int eh_ws_error(const eh_ws_layout* lay, void* d_ws, int* err, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws && err, "ws_error: null argument");
+    uint32_t v = 0;
+    EH_CUDA(cudaMemcpyAsync(&v, ws_error(d_ws, *lay), sizeof(v), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    EH_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    *err = (int)v;
+    return EH_OK;
+}

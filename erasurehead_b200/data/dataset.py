@@ -1,0 +1,106 @@
+"""In-memory dataset: equal-sized row partitions + a held-out test set.
+
+Mirrors what the reference keeps on disk under ``<input_dir>/<dataset>/<n_workers>/``
+(``1.dat`` .. ``n.dat`` or ``.npz``, ``label.dat``, ``test_data.*``, ``label_test.dat``;
+SURVEY 2.7).  One-hot data are held in ELL form (``idx[rows, nnz]`` int32, every value 1.0)
+because every row of the reference's one-hot pipeline has the same number of non-zeros
+(arrange_real_data.py:41-64).
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+from scipy.sparse import csr_matrix, issparse, vstack as sp_vstack
+
+from ..utils import io
+
+
+@dataclass
+class Dataset:
+    parts: List            # per partition: ndarray [rows, d] or csr_matrix
+    y: np.ndarray          # labels of all partitions, concatenated in partition order
+    X_test: object
+    y_test: np.ndarray
+    n_cols: int
+    rows_per_part: int
+    name: str = "synthetic"
+
+    @property
+    def n_partitions(self) -> int:
+        return len(self.parts)
+
+    @property
+    def is_sparse(self) -> bool:
+        return issparse(self.parts[0])
+
+    def partition(self, p: int):
+        return self.parts[p]
+
+    def labels(self, p: int) -> np.ndarray:
+        r = self.rows_per_part
+        return self.y[p * r:(p + 1) * r]
+
+    def train_matrix(self, compat_skip_last: bool = False):
+        """All training rows.  ``compat_skip_last`` reproduces Q1 (naive.py:159-172: the
+        evaluation loop ``range(2, n_procs-1)`` never loads the last partition)."""
+        parts = self.parts[:-1] if compat_skip_last and len(self.parts) > 1 else self.parts
+        X = sp_vstack(parts).tocsr() if self.is_sparse else np.vstack(parts)
+        return X, self.y[:X.shape[0]]
+
+    def ell(self, p: Optional[int] = None, test: bool = False) -> np.ndarray:
+        """``[rows, nnz]`` int32 column indices of a one-hot partition (all values must be 1)."""
+        X = self.X_test if test else self.parts[p]
+        return csr_to_ell(X)
+
+    def save(self, out_dir: str) -> None:
+        io.ensure_dir(out_dir)
+        for k, X in enumerate(self.parts, start=1):
+            if issparse(X):
+                io.save_sparse_csr(os.path.join(out_dir, str(k)), X)
+            else:
+                io.save_matrix(X, os.path.join(out_dir, f"{k}.dat"))
+        io.save_vector(self.y, os.path.join(out_dir, "label.dat"))
+        io.save_vector(self.y_test, os.path.join(out_dir, "label_test.dat"))
+        if issparse(self.X_test):
+            io.save_sparse_csr(os.path.join(out_dir, "test_data"), self.X_test)
+        else:
+            io.save_matrix(self.X_test, os.path.join(out_dir, "test_data.dat"))
+
+
+def csr_to_ell(X) -> np.ndarray:
+    X = csr_matrix(X)
+    nnz = np.diff(X.indptr)
+    if nnz.size == 0 or nnz.min() != nnz.max():
+        raise ValueError("ELL needs a constant number of non-zeros per row")
+    if not np.all(X.data == 1.0):
+        raise ValueError("ELL one-hot format needs all values == 1")
+    return X.indices.reshape(X.shape[0], int(nnz[0])).astype(np.int32)
+
+
+def ell_to_csr(idx: np.ndarray, n_cols: int) -> csr_matrix:
+    rows, k = idx.shape
+    return csr_matrix((np.ones(rows * k), idx.reshape(-1), np.arange(0, rows * k + 1, k)),
+                      shape=(rows, n_cols))
+
+
+def load_dataset(data_dir: str, n_partitions: int, is_real: bool, n_cols: int,
+                 rows_per_part: Optional[int] = None) -> Dataset:
+    """Read the reference directory layout (approximate_coding.py:39-69)."""
+    parts = []
+    for k in range(1, n_partitions + 1):
+        if is_real:
+            parts.append(io.load_sparse_csr(os.path.join(data_dir, str(k))))
+        else:
+            parts.append(np.atleast_2d(io.load_data(os.path.join(data_dir, f"{k}.dat"))))
+    y = np.atleast_1d(io.load_data(os.path.join(data_dir, "label.dat")))
+    y_test = np.atleast_1d(io.load_data(os.path.join(data_dir, "label_test.dat")))
+    if is_real:
+        X_test = io.load_sparse_csr(os.path.join(data_dir, "test_data"))
+    else:
+        X_test = np.atleast_2d(io.load_data(os.path.join(data_dir, "test_data.dat")))
+    rpp = rows_per_part or parts[0].shape[0]
+    return Dataset(parts=parts, y=y, X_test=X_test, y_test=y_test, n_cols=n_cols,
+                   rows_per_part=rpp, name=os.path.basename(os.path.normpath(data_dir)))

@@ -1,0 +1,423 @@
+"""The training engine: one code path for all seven schemes, two models, GD/AGD.
+
+Reference counterpart: the ten ``*_logistic_regression`` / ``*_linear_regression`` drivers
+ -- data assignment, master loop, worker loop and evaluation epilogue each.  Here
+
+* the scheme is a :class:`~erasurehead_b200.schemes.SchemeSpec` row;
+* worker compute + encode + ship is one fused kernel per message (``csrc/grad_dense.cu`` /
+  ``grad_ell.cu``), the master side is one decoder kernel per round (``csrc/decoder.cu``);
+* the round loop itself runs natively (``eh_run_rounds``): the host enqueues all rounds and
+  synchronises once; ordering between GPUs is carried by stamped flags in peer-mapped memory.
+
+``Engine(device='cpu')`` (or a machine without CUDA) executes the float64 oracle instead, so
+the CLI, result writers, checkpointing and multi-process host logic are testable anywhere.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import time
+from math import comb
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from . import codes, oracle
+from .config import RunConfig
+from .delays import delay_table
+from .models import get_model
+from .parallel.context import DistContext, init_distributed
+from .schemes import (DECODE_LSTSQ, MSG_CODED, MSG_PRIVATE, SchemeSpec, build_scheme)
+
+NEVER_NS = (1 << 64) - 1
+DECODE_TABLE_LIMIT = 50000        # rows of the precomputed decode table (C(n, s))
+
+
+def _pad32(d: int) -> int:
+    return (d + 31) // 32 * 32
+
+
+class Engine:
+    """Owns the device state of one run on one rank."""
+
+    def __init__(self, cfg: RunConfig, data=None, ctx: Optional[DistContext] = None,
+                 device: Optional[str] = None, delays: Optional[np.ndarray] = None):
+        self.cfg = cfg
+        self.ctx = ctx or init_distributed(device)
+        self.model = get_model(cfg.model_name, cfg.classes)
+        # the code matrix must be identical on every rank: seed it, or let the root draw it
+        B = None
+        if cfg.seed is None and cfg.scheme in ("coded", "partial_coded"):
+            B = self.ctx.broadcast_object(
+                codes.cyclic_code(cfg.n_workers, cfg.n_stragglers) if self.ctx.is_root else None)
+        self.spec: SchemeSpec = build_scheme(cfg, B)
+        self.data = data
+        self.first_round = 0
+        self.on_gpu = self.ctx.device.type == "cuda"
+        beta0 = oracle.initial_beta(self.spec, cfg.n_cols, cfg.seed, self.model.n_out)
+        self.beta0 = self.ctx.broadcast_object(beta0 if self.ctx.is_root else None)
+        self.u0 = np.zeros_like(self.beta0)
+        if cfg.resume:
+            self._load_checkpoint(cfg.resume)
+        # delay rows are indexed by (round - first_round); the stream is a function of the round
+        self.delays = delays if delays is not None else delay_table(
+            cfg.rounds - self.first_round, self.spec.n, mode=cfg.delay_mode, scale=cfg.delay_scale,
+            n_stragglers=cfg.n_stragglers, fixed_sleep=cfg.delay_fixed, enabled=bool(cfg.add_delay),
+            first_round=self.first_round)
+        self.result: Optional[oracle.RunResult] = None
+        self.launches = 0
+        if self.on_gpu:
+            if self.model.n_out != 1:
+                raise NotImplementedError(
+                    "multi-column (softmax) models run through ops.softmax / the CPU engine in this round")
+            self._setup_gpu()
+
+    # ------------------------------------------------------------------ device set-up
+    def _setup_gpu(self) -> None:
+        import torch
+        from .ops import _lib, grad as gops
+        from .parallel.workspace import Workspace
+
+        cfg, spec, ctx = self.cfg, self.spec, self.ctx
+        dev = ctx.device
+        self.torch = torch
+        L = _lib.lib()
+        d = cfg.n_cols
+        self.ws = Workspace(ctx, spec.n, spec.n_msgs, d)
+        lay = self.ws.lay
+        # ---- partitions resident on this GPU (deduplicated across local workers)
+        self.parts: Dict[int, tuple] = {}
+        mine = ctx.local_workers(spec.n)
+        needed = sorted({sg.partition for w in mine for sg in spec.segments[w]})
+        self.sparse = bool(self.data.is_sparse) if self.data is not None else False
+        for p in needed:
+            self.parts[p] = self._device_partition(p)
+        # ---- worker jobs (private message first: it is sent first, partial_coded.py:229,234)
+        jobs = []
+        for w in mine:
+            for kind in (MSG_PRIVATE, MSG_CODED):
+                segs = [sg for sg in spec.segments[w] if sg.msg == kind]
+                if not segs:
+                    continue
+                for c0 in range(0, len(segs), _lib.EH_MAX_SEGS):
+                    if c0 > 0:
+                        raise NotImplementedError(
+                            f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
+                            "use fewer partitions per worker")
+                j = _lib.WorkerJob()
+                j.worker, j.msg, j.sparse, j.model = w, kind, int(self.sparse), self.model.device_id
+                j.n_segs, j.rows_per_seg, j.d = len(segs), spec.rows_per_part, d
+                X0 = self.parts[segs[0].partition][0]
+                j.ld_or_nnz = X0.shape[1] if self.sparse else X0.stride(0)
+                j.bias_col = (d - 1) if self.sparse else -1
+                for i, sg in enumerate(segs):
+                    Xp, yp = self.parts[sg.partition]
+                    j.d_X[i], j.d_y[i], j.coeff[i] = Xp.data_ptr(), yp.data_ptr(), float(sg.coeff)
+                jobs.append(j)
+        self._jobs = (_lib.WorkerJob * max(1, len(jobs)))(*jobs)
+        self.n_jobs = len(jobs)
+        ld_max = max([_pad32(d)] + [self.parts[p][0].stride(0) for p in needed if not self.sparse])
+        sb = max(L.eh_grad_dense_scratch_bytes(int(ld_max)), L.eh_grad_ell_scratch_bytes(int(d)))
+        self.scratch = gops.Scratch(sb, dev)
+        self.timeout_ns = int(120e9)
+        # ---- decoder state (root)
+        self.dec = None
+        if ctx.is_root:
+            self._setup_decoder()
+        plan = _lib.RoundPlan()
+        plan.n_jobs = self.n_jobs
+        plan.jobs = C.cast(self._jobs, C.POINTER(_lib.WorkerJob))
+        plan.d_ws_local, plan.d_ws_root = self.ws.local, self.ws.root
+        plan.d_scratch, plan.scratch_bytes = self.scratch.ptr(), self.scratch.nbytes
+        plan.decoder = C.pointer(self.dec) if self.dec is not None else None
+        plan.timeout_ns = self.timeout_ns
+        plan.lay = lay
+        self.plan = plan
+
+    def _device_partition(self, p: int):
+        """(X or ELL idx, y) of partition ``p`` on this GPU, float32 / int32."""
+        torch = self.torch
+        dev = self.ctx.device
+        cfg, spec = self.cfg, self.spec
+        if self.data is None:
+            if not cfg.synthetic:
+                raise ValueError("no dataset given and cfg.synthetic is off")
+            from .ops import synth
+            task = 1 if self.model.name == "linear" else 0
+            return synth.synth_gmm(spec.rows_per_part, cfg.n_cols, cfg.seed or 0, p, task, dev)
+        y = torch.as_tensor(np.ascontiguousarray(self.data.labels(p)), dtype=torch.float32).to(dev)
+        if self.sparse:
+            idx = torch.from_numpy(np.ascontiguousarray(self.data.ell(p))).to(dev)
+            return idx, y
+        Xh = np.asarray(self.data.partition(p), dtype=np.float32)
+        ld = _pad32(cfg.n_cols)
+        X = torch.zeros((Xh.shape[0], ld), dtype=torch.float32, device=dev)
+        X[:, :cfg.n_cols] = torch.from_numpy(Xh).to(dev)
+        return X, y
+
+    def _setup_decoder(self) -> None:
+        torch = self.torch
+        from .ops import _lib, codegen
+        cfg, spec, dev = self.cfg, self.spec, self.ctx.device
+        n, d, R = spec.n, cfg.n_cols, cfg.rounds
+        t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(dev)
+        self.t_group = t(spec.group_of, torch.int32)
+        self.t_B = t(spec.B, torch.float64) if spec.B is not None else None
+        self.t_A = self.t_binom = None
+        use_table = (spec.decode == DECODE_LSTSQ and cfg.decode != "solve"
+                     and comb(n, spec.s) <= DECODE_TABLE_LIMIT)
+        if cfg.decode == "table" and spec.decode == DECODE_LSTSQ and not use_table:
+            raise ValueError("decode table too large; use --decode=solve")
+        if use_table:
+            self.t_A = codegen.decode_table(self.t_B, spec.s)
+            self.t_binom = t(codes.binomial_table(n), torch.int64)
+        dl = np.where(np.isfinite(self.delays), np.minimum(self.delays, 1e6) * 1e9, 0).astype(np.uint64)
+        dl[~np.isfinite(self.delays)] = np.uint64(NEVER_NS)
+        self.t_delay = torch.from_numpy(dl.view(np.int64)).to(dev)
+        self.t_eta = t(cfg.learning_rates(), torch.float64)
+        self.t_beta64 = t(self.beta0, torch.float64)
+        self.t_u64 = t(self.u0, torch.float64)
+        self.t_betaset = torch.zeros((R, d), dtype=torch.float64, device=dev)
+        self.t_timeset = torch.zeros(R, dtype=torch.float64, device=dev)
+        self.t_wts = torch.full((R, n), -1.0, dtype=torch.float64, device=dev)
+        self.t_weights = torch.zeros((R, n), dtype=torch.float64, device=dev)
+        self.t_ncol = torch.zeros(R, dtype=torch.int32, device=dev)
+        self.t_tstart = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.t_decscratch = torch.zeros((_lib.lib().eh_decoder_scratch_bytes() + 7) // 8, dtype=torch.int64, device=dev)
+        D = _lib.DecoderDesc()
+        D.n_workers, D.n_msgs, D.n_groups, D.s = n, spec.n_msgs, spec.n_groups, spec.s
+        D.need_private, D.need_count, D.need_groups, D.decode = (spec.need_private, spec.need_count,
+                                                                 spec.need_groups, spec.decode)
+        D.d, D.d_pad = d, self.ws.lay.d_pad
+        D.update_agd = int(cfg.update_rule == "AGD")
+        D.n_peers = self.ctx.world
+        D.d_group_of = self.t_group.data_ptr()
+        D.d_B = self.t_B.data_ptr() if self.t_B is not None else None
+        D.d_A = self.t_A.data_ptr() if self.t_A is not None else None
+        D.d_binom = self.t_binom.data_ptr() if self.t_binom is not None else None
+        D.d_delay_ns, D.d_eta = self.t_delay.data_ptr(), self.t_eta.data_ptr()
+        D.d_beta64, D.d_u64 = self.t_beta64.data_ptr(), self.t_u64.data_ptr()
+        D.d_ws_local = self.ws.local
+        for r in range(self.ctx.world):
+            D.d_ws_peer[r] = self.ws.peers[r]
+        D.d_betaset, D.d_timeset = self.t_betaset.data_ptr(), self.t_timeset.data_ptr()
+        D.d_worker_timeset, D.d_weights = self.t_wts.data_ptr(), self.t_weights.data_ptr()
+        D.d_ncollected, D.d_tstart = self.t_ncol.data_ptr(), self.t_tstart.data_ptr()
+        D.d_scratch = self.t_decscratch.data_ptr()
+        D.alpha, D.n_rows, D.lr_scale = float(cfg.alpha), float(cfg.n_rows), float(spec.lr_scale)
+        D.timeout_ns = self.timeout_ns
+        D.lay = self.ws.lay
+        self.dec = D
+
+    # ------------------------------------------------------------------ running
+    def launches_per_round(self) -> int:
+        """Kernels this rank launches per round (gradient jobs + decoder on the root)."""
+        return self.n_jobs + (1 if self.ctx.is_root else 0) if self.on_gpu else 0
+
+    def prepare(self) -> None:
+        """Reset flags and publish the initial parameters (untimed set-up of a run)."""
+        if not self.on_gpu:
+            return
+        from .ops import _lib
+        self.ws.reset()
+        self.scratch.zero_()
+        if self.dec is not None:
+            self.t_decscratch.zero_()
+        self.torch.cuda.synchronize()
+        self.ctx.barrier()
+        if self.dec is not None:
+            _lib.check(_lib.lib().eh_decoder_publish(C.byref(self.dec), self.first_round, _lib.stream_ptr()),
+                       "eh_decoder_publish")
+        self._cursor = self.first_round
+
+    def enqueue(self, n_rounds: int) -> None:
+        """Enqueue ``n_rounds`` further rounds on the current stream (no synchronisation)."""
+        from .ops import _lib
+        r0 = self._cursor - self.first_round
+        _lib.check(_lib.lib().eh_run_rounds(C.byref(self.plan), self._cursor, n_rounds, r0, _lib.stream_ptr()),
+                   "eh_run_rounds")
+        self._cursor += n_rounds
+        self.launches += n_rounds * self.launches_per_round()
+
+    def step(self, delay_row: Optional[np.ndarray] = None, eta: Optional[float] = None):
+        """One round through the public streaming API (used by ``bench.py`` for the end-to-end
+        number).  The root copies this round's host inputs (the per-worker delay row and the
+        learning rate) from pinned memory to the device tables, every rank enqueues one round,
+        and the root reads the round's result -- the new iterate and the round time -- back
+        into pinned host memory.  Returns ``(beta[d] float64, seconds)`` on the root, else None.
+        Call :meth:`prepare` once before the first step."""
+        torch = self.torch
+        r = self._cursor - self.first_round
+        if self.dec is not None:
+            if not hasattr(self, "_pin_in"):
+                n, d = self.spec.n, self.cfg.n_cols
+                self._pin_in = torch.empty(n + 1, dtype=torch.int64).pin_memory()
+                self._pin_out = torch.empty(d + 1, dtype=torch.float64).pin_memory()
+                self.h2d_bytes = (n + 1) * 8
+                self.d2h_bytes = (d + 1) * 8
+            n = self.spec.n
+            row = self.delays[r] if delay_row is None else np.asarray(delay_row, dtype=np.float64)
+            ns = np.where(np.isfinite(row), np.minimum(row, 1e6) * 1e9, 0).astype(np.uint64)
+            ns[~np.isfinite(row)] = np.uint64(NEVER_NS)
+            self._pin_in[:n] = torch.from_numpy(ns.view(np.int64))
+            e = float(self.cfg.learning_rates()[self._cursor] if eta is None else eta)
+            self._pin_in[n:] = torch.from_numpy(np.array([e], dtype=np.float64).view(np.int64))
+            self.t_delay[r].copy_(self._pin_in[:n], non_blocking=True)
+            self.t_eta[r:r + 1].view(torch.int64).copy_(self._pin_in[n:], non_blocking=True)
+        self.enqueue(1)
+        if self.dec is not None:
+            d = self.cfg.n_cols
+            self._pin_out[:d].copy_(self.t_betaset[r], non_blocking=True)
+            self._pin_out[d:].copy_(self.t_timeset[r:r + 1], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return self._pin_out[:d].numpy(), float(self._pin_out[d])
+        return None
+
+    def finish(self) -> None:
+        self.torch.cuda.synchronize()
+        err = self.ws.error()
+        errs = self.ctx.all_gather_object(err)
+        if any(errs):
+            raise RuntimeError(f"device watchdog fired (per-rank error words {errs}); "
+                               "a worker died or a stop rule became unsatisfiable")
+
+    def run(self, rounds: Optional[int] = None) -> Optional[oracle.RunResult]:
+        """Run ``rounds`` rounds (default: all remaining).  Returns the result on the root."""
+        cfg = self.cfg
+        R = (cfg.rounds - self.first_round) if rounds is None else rounds
+        t0 = time.time()
+        if not self.on_gpu:
+            res = None
+            if self.ctx.is_root:
+                res = oracle.run_rounds(cfg, self.spec, self.data, self.delays[:R], beta0=self.beta0, u0=self.u0,
+                                        first_round=self.first_round, rounds=R, model=self.model)
+                res.wall_time = time.time() - t0
+            self.result = res
+            self.ctx.barrier()
+            return res
+        self.prepare()
+        chunk = cfg.checkpoint_every if cfg.checkpoint_every > 0 else R
+        done = 0
+        while done < R:
+            k = min(chunk, R - done)
+            self.enqueue(k)
+            self.finish()
+            done += k
+            if cfg.checkpoint_every > 0 and self.ctx.is_root:
+                self.save_checkpoint(self._ckpt_path(), self.first_round + done)
+        self.ctx.barrier()
+        res = self._collect(R) if self.ctx.is_root else None
+        if res is not None:
+            res.wall_time = time.time() - t0
+        self.result = res
+        return res
+
+    def _collect(self, R: int) -> oracle.RunResult:
+        cpu = lambda t: t[:R].detach().cpu().numpy()
+        return oracle.RunResult(
+            betaset=cpu(self.t_betaset), timeset=cpu(self.t_timeset), worker_timeset=cpu(self.t_wts),
+            weights=cpu(self.t_weights), n_collected=cpu(self.t_ncol).astype(np.int64),
+            u=self.t_u64.cpu().numpy(), beta=self.t_beta64.cpu().numpy())
+
+    # ------------------------------------------------------------------ evaluation
+    def evaluate(self, res: Optional[oracle.RunResult] = None):
+        """Train/test loss (or MSE) and test AUC of every stored iterate (root only)."""
+        from . import results
+        res = res or self.result
+        if not self.ctx.is_root or res is None:
+            return None
+        if not self.on_gpu:
+            return results.evaluate_host(self.model, self.data, res.betaset, self.cfg.compat)
+        return self._evaluate_gpu(res.betaset)
+
+    def _evaluate_gpu(self, betaset: np.ndarray):
+        from . import results
+        from .ops import metrics as mops
+        torch = self.torch
+        dev = self.ctx.device
+        cfg, spec = self.cfg, self.spec
+        R, d = betaset.shape
+        Bt = torch.zeros((R, _pad32(d)), dtype=torch.float32, device=dev)
+        Bt[:, :d] = torch.from_numpy(betaset).to(dev)
+        kind = 1 if self.model.name == "linear" else 0
+        n_parts = spec.n_partitions - (1 if cfg.compat and spec.n_partitions > 1 else 0)   # Q1
+        tr = torch.zeros(R, dtype=torch.float64, device=dev)
+        rows = 0
+        for p in range(n_parts):
+            Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
+            P = mops.margins_ell(Xp, Bt) if self.sparse else mops.margins_dense(Xp, Bt, d)
+            tr += mops.loss_columns(P, yp, kind) * Xp.shape[0]
+            rows += Xp.shape[0]
+            del P
+        tr /= rows
+        Xt, yt = self._device_test()
+        Pt = mops.margins_ell(Xt, Bt) if self.sparse else mops.margins_dense(Xt, Bt, d)
+        te = mops.loss_columns(Pt, yt, kind)
+        auc = None
+        if self.model.has_auc:
+            Pcol = Pt.t().contiguous()
+            auc = torch.stack([mops.auc(Pcol[i], yt) for i in range(R)]).cpu().numpy()
+        return results.Evaluation(tr.cpu().numpy(), te.cpu().numpy(), auc)
+
+    def _device_test(self):
+        torch = self.torch
+        dev = self.ctx.device
+        cfg = self.cfg
+        if self.data is None:
+            from .ops import synth
+            task = 1 if self.model.name == "linear" else 0
+            n_test = max(1, int(0.2 * cfg.n_rows))                         # generate_data.py:40
+            return synth.synth_gmm(n_test, cfg.n_cols, cfg.seed or 0, (1 << 40), task, dev)
+        yt = torch.as_tensor(np.ascontiguousarray(self.data.y_test), dtype=torch.float32).to(dev)
+        if self.sparse:
+            return torch.from_numpy(np.ascontiguousarray(self.data.ell(test=True))).to(dev), yt
+        Xh = np.asarray(self.data.X_test, dtype=np.float32)
+        X = torch.zeros((Xh.shape[0], _pad32(cfg.n_cols)), dtype=torch.float32, device=dev)
+        X[:, :cfg.n_cols] = torch.from_numpy(Xh).to(dev)
+        return X, yt
+
+    # ------------------------------------------------------------------ checkpoint / resume
+    def _ckpt_path(self) -> str:
+        from .utils import io
+        return io.ensure_dir(self.cfg.results_dir) + f"{self.spec.prefix}_checkpoint.npz"
+
+    def save_checkpoint(self, path: str, next_round: int) -> None:
+        """Persist ``(next round, beta, u, B)``; the delay stream is a pure function of the round
+        index so no RNG state is needed (delays.py)."""
+        if self.on_gpu:
+            beta, u = self.t_beta64.cpu().numpy(), self.t_u64.cpu().numpy()
+        else:
+            beta, u = self.result.beta, self.result.u
+        np.savez(path, next_round=next_round, beta=beta, u=u,
+                 B=self.spec.B if self.spec.B is not None else np.zeros((0, 0)),
+                 scheme=self.spec.name, update_rule=self.cfg.update_rule)
+
+    def _load_checkpoint(self, path: str) -> None:
+        ck = np.load(path, allow_pickle=False)
+        if str(ck["scheme"]) != self.spec.name:
+            raise ValueError(f"checkpoint is for scheme {ck['scheme']}, not {self.spec.name}")
+        self.first_round = int(ck["next_round"])
+        self.beta0, self.u0 = ck["beta"], ck["u"]
+        if ck["B"].size:
+            self.spec = build_scheme(self.cfg, ck["B"])
+
+    # ------------------------------------------------------------------ observability
+    def write_metrics_jsonl(self, path: str, res: oracle.RunResult, ev=None) -> None:
+        with open(path, "w") as f:
+            for r in range(len(res.timeset)):
+                rec = {"round": self.first_round + r, "time_s": float(res.timeset[r]),
+                       "n_collected": int(res.n_collected[r]),
+                       "arrived_mask": int(sum(1 << w for w in np.flatnonzero(res.worker_timeset[r] >= 0))),
+                       "weights": [float(x) for x in res.weights[r]]}
+                if ev is not None:
+                    rec["train_loss"] = float(ev.training_loss[r])
+                    rec["test_loss"] = float(ev.testing_loss[r])
+                    if ev.auc is not None:
+                        rec["auc"] = float(ev.auc[r])
+                f.write(json.dumps(rec) + "\n")
+
+    def close(self) -> None:
+        if self.on_gpu and getattr(self, "ws", None) is not None:
+            self.torch.cuda.synchronize()
+            self.ws.close()
+            self.ws = None

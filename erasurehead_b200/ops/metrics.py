@@ -1,0 +1,48 @@
+"""Evaluation operators on the device (reference epilogue naive.py:154-209, util.py:136-141)."""
+from __future__ import annotations
+
+import torch
+
+from ._lib import check, lib, stream_ptr
+
+
+def margins_dense(X: torch.Tensor, Bt: torch.Tensor, d: int | None = None) -> torch.Tensor:
+    """``P[rows, R] = X[:, :d] @ Bt[:, :d].T`` for all ``R`` stored iterates at once."""
+    assert X.dtype == torch.float32 and Bt.dtype == torch.float32 and X.stride(1) == 1 and Bt.stride(1) == 1
+    d = int(d or Bt.shape[1])
+    R = Bt.shape[0]
+    P = torch.empty((X.shape[0], R), dtype=torch.float32, device=X.device)
+    check(lib().eh_margins_dense(X.data_ptr(), X.shape[0], d, X.stride(0), Bt.data_ptr(), R, Bt.stride(0),
+                                 P.data_ptr(), stream_ptr()), "eh_margins_dense")
+    return P
+
+
+def margins_ell(idx: torch.Tensor, Bt: torch.Tensor) -> torch.Tensor:
+    assert idx.dtype == torch.int32 and idx.is_contiguous() and Bt.dtype == torch.float32
+    R = Bt.shape[0]
+    P = torch.empty((idx.shape[0], R), dtype=torch.float32, device=idx.device)
+    check(lib().eh_margins_ell(idx.data_ptr(), idx.shape[0], idx.shape[1], Bt.data_ptr(), R, Bt.stride(0),
+                               P.data_ptr(), stream_ptr()), "eh_margins_ell")
+    return P
+
+
+def loss_columns(P: torch.Tensor, y: torch.Tensor, kind: int) -> torch.Tensor:
+    """Mean loss per column of ``P`` (kind 0: logistic with labels +-1; 1: squared error)."""
+    assert P.is_contiguous() and P.dtype == torch.float32 and y.dtype == torch.float32
+    out = torch.zeros(P.shape[1], dtype=torch.float64, device=P.device)
+    check(lib().eh_loss_columns(P.data_ptr(), y.data_ptr(), P.shape[0], P.shape[1], int(kind), out.data_ptr(),
+                                stream_ptr()), "eh_loss_columns")
+    return out / P.shape[0]
+
+
+def auc(scores: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """Tie-aware ROC-AUC of one score vector (labels +1/-1) -> 0-d float64 tensor."""
+    scores = scores.contiguous().float()
+    labels = labels.contiguous().float()
+    n = scores.numel()
+    nbytes = lib().eh_auc_scratch_bytes(n)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=scores.device)
+    out = torch.empty((), dtype=torch.float64, device=scores.device)
+    check(lib().eh_auc(scores.data_ptr(), labels.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), nbytes,
+                       stream_ptr()), "eh_auc")
+    return out

@@ -1,0 +1,69 @@
+"""Peer-mapped workspace: the NVLink replacement for the reference's MPI message buffers.
+
+Every GPU allocates one block (layout in ``include/erasurehead.h``) holding the double-buffered
+parameters, the parameter flag, and -- used on the root only -- the per-(worker, message)
+gradient slots with their arrival flags.  CUDA IPC handles are exchanged once through
+``torch.distributed``; afterwards
+
+* every worker GPU stores its encoded gradient straight into the *root's* slot and releases the
+  arrival flag (replaces ``comm.Isend([g, MPI.DOUBLE], dest=0, tag=i)``, naive.py:150);
+* the root stores new parameters into *every* GPU's buffer and releases the parameter flag
+  (replaces the ``Isend(beta)`` loop, naive.py:97-98).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List
+
+from ..ops._lib import WsLayout, check, lib, stream_ptr
+from .context import DistContext
+
+
+class Workspace:
+    def __init__(self, ctx: DistContext, n_workers: int, n_msgs: int, d: int):
+        self.ctx = ctx
+        L = lib()
+        self.lay = WsLayout()
+        check(L.eh_ws_layout_make(n_workers, n_msgs, d, C.byref(self.lay)), "eh_ws_layout_make")
+        self._local = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        check(L.eh_ws_create(C.byref(self.lay), C.byref(self._local), handle), "eh_ws_create")
+        self.local = self._local.value
+        self._opened: List[int] = []
+        handles = ctx.all_gather_object(bytes(handle.raw))
+        # root maps every peer (parameter push); everyone maps the root (gradient ship)
+        self.peers: List[int] = [0] * ctx.world
+        self.peers[ctx.rank] = self.local
+        if ctx.world > 1:
+            want = range(ctx.world) if ctx.is_root else [0]
+            for r in want:
+                if r == ctx.rank:
+                    continue
+                p = C.c_void_p()
+                check(L.eh_ws_open(handles[r], C.byref(p)), f"eh_ws_open(rank {r})")
+                self.peers[r] = p.value
+                self._opened.append(p.value)
+        self.root = self.peers[0]
+
+    def reset(self) -> None:
+        check(lib().eh_ws_reset(C.byref(self.lay), self.local, stream_ptr()), "eh_ws_reset")
+
+    def error(self) -> int:
+        e = C.c_int(0)
+        check(lib().eh_ws_error(C.byref(self.lay), self.local, C.byref(e), stream_ptr()), "eh_ws_error")
+        return e.value
+
+    def close(self) -> None:
+        L = lib()
+        for p in self._opened:
+            L.eh_ws_close(p)
+        self._opened = []
+        if self.local:
+            L.eh_ws_destroy(self.local)
+            self.local = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

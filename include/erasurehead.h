@@ -1,0 +1,245 @@
+/*
+ * erasurehead.h -- C ABI of liberasurehead.so (sm_100a).
+ *
+ * Every entry point returns 0 on success, a positive cudaError_t, or a negative EH_E* code;
+ * eh_last_error() gives a human-readable message for the calling thread's last failure.
+ * Pointers named d_* are device pointers (possibly peer-mapped), h_* are host pointers.
+ * All launches go to the cudaStream_t passed as `stream` (a void* here so the header needs no
+ * CUDA include); nothing synchronises unless documented.
+ *
+ * Reference citations (`file:line`) point into Distributed-Deep-Learning/ErasureHead.
+ */
+#ifndef ERASUREHEAD_H_
+#define ERASUREHEAD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EH_OK            0
+#define EH_EINVAL       -1   /* bad argument / unsupported shape */
+#define EH_ETIMEOUT     -2   /* device-side watchdog fired */
+#define EH_ENOTSUP      -3
+#define EH_ESTATE       -4
+
+/* model ids (erasurehead_b200/models/base.py) */
+#define EH_MODEL_LOGISTIC 0
+#define EH_MODEL_LINEAR   1
+
+/* decode kinds (erasurehead_b200/schemes.py) */
+#define EH_DECODE_SUM             0
+#define EH_DECODE_FIRST_PER_GROUP 1
+#define EH_DECODE_LSTSQ           2
+
+/* message kinds */
+#define EH_MSG_CODED   0
+#define EH_MSG_PRIVATE 1
+
+#define EH_MAX_WORKERS 64
+#define EH_MAX_MSGS     2
+#define EH_MAX_PEERS   16
+
+const char* eh_last_error(void);
+int  eh_version(void);
+/* SM count / co-resident CTA capacity of the current device for the persistent kernels. */
+int  eh_device_info(int* sm_count, int* grad_dense_ctas, int* decoder_ctas);
+
+/* ------------------------------------------------------------------------------------------
+ * Workspace: one cudaMalloc'd block per GPU that peers map through CUDA IPC.  Holds the
+ * double-buffered parameters, the gradient-message slots and all flags.
+ * Replaces the reference's mpi4py Isend/Irecv buffers (naive.py:68-79).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct eh_ws_layout {
+    uint64_t bytes;          /* total size */
+    uint64_t off_ctl;        /* eh control words (see csrc/workspace.cuh) */
+    uint64_t off_beta;       /* float  [2][d_pad]                      */
+    uint64_t off_flags;      /* uint32 [n_workers][EH_MAX_MSGS], padded to 128 B each */
+    uint64_t off_slots;      /* float  [n_workers][n_msgs][2][d_pad]   */
+    uint32_t n_workers, n_msgs, d_pad, reserved;
+} eh_ws_layout;
+
+int eh_ws_layout_make(int n_workers, int n_msgs, int d, eh_ws_layout* out);
+int eh_ws_create(const eh_ws_layout* lay, void** d_ws, unsigned char ipc_handle[64]);
+int eh_ws_open(const unsigned char ipc_handle[64], void** d_ws_peer);
+int eh_ws_close(void* d_ws_peer);
+int eh_ws_destroy(void* d_ws);
+int eh_ws_reset(const eh_ws_layout* lay, void* d_ws, void* stream);
+/* Read the sticky device error word (0 = none) -- set by any watchdog. */
+int eh_ws_error(const eh_ws_layout* lay, void* d_ws, int* err, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K1+K2'+K3 fused: encoded partial gradient of one worker message, dense fp32 features.
+ *   g = sum_segs coeff[seg] * sum_rows  X_seg[r,:] * resid(X_seg[r,:].beta, y_seg[r])
+ * logistic: resid = -y/(exp(p*y)+1) (naive.py:137-139, encode fold coded.py:92-95,184);
+ * linear:   resid = -2 (y-p)        (naive.py:345-346).
+ * X is streamed once from HBM by TMA bulk copies into a shared-memory ring; the row tile
+ * stays on chip between the forward dot and the rank-1 accumulate.  Per-CTA partial sums are
+ * combined through `d_scratch` (>= eh_grad_dense_scratch_bytes) by a device-wide barrier and
+ * the result is written to `d_out` (local or peer memory).  If `d_flag` is non-NULL the kernel
+ * first waits for the parameter flag (`d_beta_flag`, value >= stamp) and, once `d_out` is
+ * complete, publishes `stamp` to `d_flag` with release/system semantics.
+ * ---------------------------------------------------------------------------------------- */
+#define EH_MAX_SEGS 16
+
+typedef struct eh_grad_job {
+    const float*    d_X[EH_MAX_SEGS];   /* per segment: [rows_per_seg, ld] row-major fp32, 16B aligned */
+    const float*    d_y[EH_MAX_SEGS];   /* per segment: [rows_per_seg] labels / targets */
+    float           coeff[EH_MAX_SEGS]; /* per segment encode weight (B[w, partition] or 1) */
+    const float*    d_beta;         /* [d] parameters (buffer of this round) */
+    float*          d_out;          /* [d] destination (may be peer memory) */
+    uint32_t*       d_flag;         /* arrival flag to publish (may be peer memory) or NULL */
+    const uint32_t* d_beta_flag;    /* local parameter flag to wait on, or NULL */
+    uint32_t*       d_err;          /* sticky error word or NULL */
+    int32_t         n_segs;         /* partitions streamed for this message (<= EH_MAX_SEGS) */
+    int32_t         rows_per_seg;
+    int32_t         d, ld;          /* ld % 4 == 0, ld >= d, columns d..ld must be zero */
+    int32_t         model;
+    uint32_t        stamp;          /* round + 1 */
+    uint64_t        timeout_ns;     /* watchdog for the beta wait (0 = 30 s) */
+} eh_grad_job;
+
+size_t eh_grad_dense_scratch_bytes(int d);
+int eh_grad_dense(const eh_grad_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
+
+/* One-hot ELL features (every value 1.0; arrange_real_data.py:41-64): gather-sum margins,
+ * scatter-add gradient with the always-on bias column reduced in registers. */
+typedef struct eh_grad_ell_job {
+    const int32_t*  d_idx[EH_MAX_SEGS]; /* per segment: [rows_per_seg, nnz] column ids */
+    const float*    d_y[EH_MAX_SEGS];
+    float           coeff[EH_MAX_SEGS];
+    const float*    d_beta;
+    float*          d_out;
+    uint32_t*       d_flag;
+    const uint32_t* d_beta_flag;
+    uint32_t*       d_err;
+    int32_t         n_segs, rows_per_seg;
+    int32_t         d, nnz;
+    int32_t         model;
+    int32_t         bias_col;       /* -1 if none */
+    uint32_t        stamp;
+    uint32_t        reserved;
+    uint64_t        timeout_ns;
+} eh_grad_ell_job;
+
+size_t eh_grad_ell_scratch_bytes(int d);
+int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Decoder round (rank 0): poll arrival flags, apply the injected per-message delay, evaluate
+ * the scheme stop rule after every arrival, derive decode weights (sum / first-per-group /
+ * least-squares row by table lookup or an in-kernel solve), combine the arrived slots, apply
+ * the GD or AGD update and push the new parameters + flag to every peer -- one kernel.
+ * Reference: master loop approximate_coding.py:136-180, decode coded.py:147-149,
+ * update naive.py:112-124.
+ * ---------------------------------------------------------------------------------------- */
+typedef struct eh_decoder_desc {
+    /* scheme */
+    int32_t  n_workers, n_msgs, n_groups, s;
+    int32_t  need_private, need_count, need_groups, decode;
+    int32_t  d, d_pad;
+    int32_t  update_agd;            /* 0 = GD, 1 = AGD */
+    int32_t  n_peers;               /* GPUs (including self) receiving the parameter push */
+    const int32_t* d_group_of;      /* [n_workers] */
+    const double*  d_B;             /* [n_workers, n_workers] row-major or NULL */
+    const double*  d_A;             /* decode table [C(n,s), n] or NULL (-> in-kernel solve) */
+    const int64_t* d_binom;         /* [(n+1), (n+2)] binomials for the combinadic rank or NULL */
+    /* per-round tables, indexed by local round r = round - first_round */
+    const uint64_t* d_delay_ns;     /* [rounds, n_workers]; UINT64_MAX = never */
+    const double*   d_eta;          /* [rounds] learning rates */
+    /* state (rank 0 memory) */
+    double*  d_beta64;              /* [d] master copy */
+    double*  d_u64;                 /* [d] AGD state */
+    void*    d_ws_local;            /* rank 0 workspace */
+    void*    d_ws_peer[EH_MAX_PEERS]; /* every rank's workspace as mapped on rank 0 ([0] = local) */
+    /* outputs */
+    double*  d_betaset;             /* [rounds, d] or NULL */
+    double*  d_timeset;             /* [rounds] seconds */
+    double*  d_worker_timeset;      /* [rounds, n_workers] seconds, -1 if not collected */
+    double*  d_weights;             /* [rounds, n_workers] decode weights applied */
+    int32_t* d_ncollected;          /* [rounds] */
+    uint64_t* d_tstart;             /* [1] round-start timestamp carried between launches */
+    void*    d_scratch;             /* >= eh_decoder_scratch_bytes() */
+    double   alpha, n_rows, lr_scale;
+    uint64_t timeout_ns;            /* watchdog for one round (0 = 60 s) */
+    eh_ws_layout lay;
+} eh_decoder_desc;
+
+size_t eh_decoder_scratch_bytes(void);
+/* round = global round index (AGD's theta uses it); r = index into the per-round tables. */
+int eh_decoder_round(const eh_decoder_desc* desc, int round, int r, void* stream);
+/* Publish beta_0 (from d_beta64) to every peer and open round `round` (flag = round+1). */
+int eh_decoder_publish(const eh_decoder_desc* desc, int round, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Native round loop: enqueue `n_rounds` complete rounds on `stream` without returning to the
+ * host in between.  Per round and per local worker message: one fused gradient kernel that
+ * waits for this round's parameters, computes the encoded gradient and ships it into the
+ * root's slot; on the root rank additionally one decoder kernel.  Plays the role of the
+ * `for i in range(rounds)` loop of every reference driver (approximate_coding.py:123-207).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct eh_worker_job {
+    int32_t  worker;                 /* global worker id (slot row on the root) */
+    int32_t  msg;                    /* EH_MSG_CODED / EH_MSG_PRIVATE */
+    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL */
+    int32_t  model;
+    int32_t  n_segs, rows_per_seg;
+    int32_t  d, ld_or_nnz;           /* dense: row stride; ELL: ones per row */
+    int32_t  bias_col, reserved;
+    const void*  d_X[EH_MAX_SEGS];   /* float* rows or int32* indices */
+    const float* d_y[EH_MAX_SEGS];
+    float    coeff[EH_MAX_SEGS];
+} eh_worker_job;
+
+typedef struct eh_round_plan {
+    int32_t  n_jobs, reserved;
+    const eh_worker_job* jobs;       /* host array */
+    void*    d_ws_local;             /* this GPU's workspace (parameters + parameter flag) */
+    void*    d_ws_root;              /* the root's workspace as mapped here (slots + arrival flags) */
+    void*    d_scratch;              /* gradient-kernel scratch (max of the per-job needs) */
+    size_t   scratch_bytes;
+    const eh_decoder_desc* decoder;  /* non-NULL on the root rank only */
+    uint64_t timeout_ns;
+    eh_ws_layout lay;
+} eh_round_plan;
+
+/* r0 = index of `first_round` in the decoder's per-round tables. */
+int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_rounds, int r0, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Evaluation (reference epilogue naive.py:154-209, util.py:136-141, sklearn roc_curve+auc).
+ * ---------------------------------------------------------------------------------------- */
+/* margins P[rows, R] = X[rows, d] . Bt[R, d]^T for all stored iterates at once. */
+int eh_margins_dense(const float* d_X, int64_t rows, int d, int ld, const float* d_Bt, int R,
+                     int ldb, float* d_P, void* stream);
+int eh_margins_ell(const int32_t* d_idx, int64_t rows, int nnz, const float* d_Bt, int R, int ldb,
+                   float* d_P, void* stream);
+/* column-wise loss of P[rows, R] against y: kind 0 = logistic, 1 = squared error; out[R] = sum.
+ * d_out must be zeroed by the caller; accumulation is in double. */
+int eh_loss_columns(const float* d_P, const float* d_y, int64_t rows, int R, int kind,
+                    double* d_out, void* stream);
+/* tie-aware ROC-AUC of one score column (labels +1/-1): device radix sort (descending) + scans,
+ * trapezoid over distinct thresholds == sklearn auc(roc_curve(y, score)) (naive.py:196-197). */
+int eh_auc(const float* d_scores, const float* d_labels, int64_t n, double* d_auc, void* d_scratch,
+           size_t scratch_bytes, void* stream);
+size_t eh_auc_scratch_bytes(int64_t n);
+
+/* ------------------------------------------------------------------------------------------
+ * Data / code generation on the device.
+ * ---------------------------------------------------------------------------------------- */
+/* GMM features + logistic labels, counter-based (Philox) so that any (partition,row,col) is
+ * reproducible on any GPU (generate_data.py:23-45, util.py:39-47). */
+int eh_synth_gmm(float* d_X, float* d_y, int64_t rows, int d, int ld, uint64_t seed,
+                 uint64_t partition, int task, void* stream);
+/* Cyclic-MDS code B from the parity matrix H (util.py:64-83): one warp per row. */
+int eh_code_cyclic(const double* d_H, int n, int s, double* d_B, void* stream);
+/* Decode table A (util.py:85-103): one warp per straggler pattern. */
+int eh_code_decode_table(const double* d_B, int n, int s, const int32_t* d_missing,
+                         int64_t n_patterns, double* d_A, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ERASUREHEAD_H_ */

@@ -1,0 +1,128 @@
+"""Full fused path on one GPU (all workers on it) against the float64 oracle."""
+import numpy as np
+import pytest
+import torch
+
+from erasurehead_b200 import Engine, RunConfig, build_scheme, oracle, triple_from_scheme
+from erasurehead_b200.data import generate_gmm, generate_onehot
+from erasurehead_b200.delays import delay_table
+
+pytestmark = pytest.mark.gpu
+
+
+def spaced_delays(rounds, n, seed=0, gap=2e-3):
+    """Per-round random arrival order with >= `gap` seconds between arrivals, so the device's
+    arrival order is exactly the table's (compute jitter is microseconds)."""
+    rng = np.random.RandomState(seed)
+    T = np.zeros((rounds, n))
+    for r in range(rounds):
+        T[r, rng.permutation(n)] = gap * (1 + np.arange(n))
+    return T
+
+
+def mk(scheme, n=8, s=1, P=0, k=0, rows=1920, d=48, rounds=6, **kw):
+    ic, pp, cv = triple_from_scheme(scheme, P)
+    return RunConfig(n + 1, rows, d, "", 0, "x", ic, s, pp, cv, k, 1, kw.pop("rule", "AGD"), rounds=rounds, **kw)
+
+
+CASES = [
+    ("naive", dict(s=0)), ("coded", dict(s=2, seed=3)), ("replication", dict(s=1)),
+    ("avoidstragg", dict(s=2)), ("approx", dict(s=1, k=5)),
+    ("partial_coded", dict(n=4, s=1, P=4, rows=12 * 160, seed=2)),
+    ("partial_replication", dict(n=4, s=1, P=4, rows=12 * 160)),
+]
+
+
+@pytest.mark.parametrize("scheme,kw", CASES)
+@pytest.mark.parametrize("rule", ["GD", "AGD"])
+def test_engine_matches_oracle(scheme, kw, rule):
+    cfg = mk(scheme, rule=rule, **kw)
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=1)
+    dl = spaced_delays(cfg.rounds, cfg.n_workers, seed=5)
+    eng = Engine(cfg, data, delays=dl)
+    assert eng.on_gpu
+    res = eng.run()
+    spec = build_scheme(cfg, eng.spec.B)
+    ref = oracle.run_rounds(cfg, spec, data, dl, beta0=eng.beta0)
+    scale = max(1.0, np.abs(ref.betaset).max())
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-4 * scale
+    assert np.array_equal(res.n_collected, ref.n_collected)
+    assert np.array_equal(res.worker_timeset >= 0, ref.worker_timeset >= 0)
+    if scheme != "partial_coded":      # device uses the first n-s coded arrivals, oracle all arrived
+        assert np.allclose(res.weights, ref.weights, atol=1e-6 * max(1, np.abs(ref.weights).max()))
+    # device timers: round time ~ injected delay of the last consumed message
+    assert np.all(res.timeset >= ref.timeset - 1e-4) and np.all(res.timeset <= ref.timeset + 5e-3)
+    ev = eng.evaluate(res)
+    from erasurehead_b200 import results
+    evh = results.evaluate_host(eng.model, data, res.betaset)
+    assert np.allclose(ev.training_loss, evh.training_loss, rtol=2e-4, atol=1e-5)
+    assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=2e-4, atol=1e-5)
+    assert np.allclose(ev.auc, evh.auc, atol=2e-3)
+    eng.close()
+
+
+def test_engine_solve_decode_equals_table():
+    cfg = mk("coded", s=2, seed=3, decode="solve")
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1)
+    dl = spaced_delays(cfg.rounds, 8, seed=9)
+    a = Engine(cfg, data, delays=dl)
+    ra = a.run()
+    b = Engine(cfg.replace(decode="table"), data, delays=dl)
+    rb = b.run()
+    assert np.allclose(ra.weights, rb.weights, rtol=1e-7, atol=1e-9)
+    assert np.allclose(ra.betaset, rb.betaset, atol=1e-9)
+    a.close(); b.close()
+
+
+def test_engine_sparse_linear_and_logistic():
+    for task, model in (("logistic", None), ("linear", "linear")):
+        cfg = mk("approx", s=1, k=6, rows=8 * 120, d=700, model=model, eta0=(0.05 if model else 10.0), is_real=1)
+        cfg.dataset = "amazon-dataset"
+        data = generate_onehot(cfg.n_rows, cfg.n_cols, 13, 8, seed=2, task=task)
+        dl = spaced_delays(cfg.rounds, 8, seed=1)
+        eng = Engine(cfg, data, delays=dl)
+        res = eng.run()
+        ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl, beta0=eng.beta0, model=eng.model)
+        assert np.abs(res.betaset - ref.betaset).max() <= 1e-3 * max(1.0, np.abs(ref.betaset).max())
+        eng.close()
+
+
+def test_dead_worker_is_tolerated_and_watchdog_fires():
+    cfg = mk("coded", s=2, seed=3)
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1)
+    dl = spaced_delays(cfg.rounds, 8, seed=2)
+    dl[:, [1, 6]] = np.inf                               # two permanently dead workers, s = 2
+    eng = Engine(cfg, data, delays=dl)
+    res = eng.run()
+    assert np.all(res.worker_timeset[:, [1, 6]] == -1)
+    ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0)
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-4 * max(1.0, np.abs(ref.betaset).max())
+    eng.close()
+    # naive cannot finish a round with a dead worker: the device watchdog must fire, not hang
+    cfg = mk("naive", s=0, rounds=2)
+    dl = np.zeros((2, 8)); dl[:, 3] = np.inf
+    eng = Engine(cfg, data, delays=dl)
+    eng.timeout_ns = eng.dec.timeout_ns = eng.plan.timeout_ns = int(0.3e9)
+    with pytest.raises(RuntimeError, match="watchdog"):
+        eng.run()
+    eng.close()
+
+
+def test_synthetic_on_device_and_checkpoint_resume(tmp_path):
+    base = dict(s=1, k=5, rows=8 * 2048, d=256, synthetic=True, seed=4, output_dir=str(tmp_path) + "/")
+    cfg = mk("approx", rounds=8, **base)
+    dl = spaced_delays(8, 8, seed=3)
+    full = Engine(cfg, None, delays=dl)
+    rf = full.run()
+    ev = full.evaluate(rf)
+    assert ev.training_loss[-1] < ev.training_loss[0] and ev.auc[-1] > 0.8
+    full.close()
+    first = Engine(mk("approx", rounds=4, **base), None, delays=dl[:4])
+    first.run()
+    ck = str(tmp_path / "ck.npz")
+    first.save_checkpoint(ck, 4)
+    first.close()
+    second = Engine(mk("approx", rounds=8, resume=ck, **base), None, delays=dl[4:])
+    r2 = second.run()
+    assert np.allclose(r2.betaset, rf.betaset[4:], atol=1e-6)
+    second.close()

@@ -1,0 +1,137 @@
+"""Numerics of every CUDA kernel against a plain PyTorch / numpy float32-64 reference."""
+import itertools
+
+import numpy as np
+import pytest
+import torch
+
+from erasurehead_b200 import codes
+from erasurehead_b200.utils import metrics as hmetrics
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def ref_grad(X, y, beta, coeff, model):
+    """fp64 torch reference of the encoded gradient (naive.py:137-139 / 345-346, coded.py:184)."""
+    X, y, beta = X.double(), y.double(), beta.double()
+    p = X @ beta
+    r = -y / (torch.exp(p * y) + 1) if model == 0 else -2 * (y - p)
+    return X.t() @ (coeff * r)
+
+
+@pytest.mark.parametrize("rows,d", [(64, 16), (1000, 100), (517, 1024), (300, 1500), (1024, 4096), (96, 8000)])
+@pytest.mark.parametrize("model", [0, 1])
+def test_grad_dense_matches_reference(rows, d, model):
+    from erasurehead_b200.ops import grad, synth
+    torch.manual_seed(rows + d)
+    ld = synth.pad_cols(d)
+    X = torch.zeros(rows, ld, device=DEV)
+    X[:, :d] = torch.randn(rows, d, device=DEV) / np.sqrt(d)
+    y = torch.where(torch.rand(rows, device=DEV) > 0.5, 1.0, -1.0) if model == 0 else torch.randn(rows, device=DEV)
+    beta = torch.randn(d, device=DEV)
+    g = grad.grad_dense(X, y, beta, coeff=(1.7,), model=model, d=d)
+    want = ref_grad(X[:, :d], y, beta, 1.7, model)
+    err = (g.double() - want).abs().max().item()
+    assert err <= 2e-4 * max(1.0, want.abs().max().item()), err
+
+
+def test_grad_dense_segments_and_repeat_calls():
+    """Several partitions with different encode weights in one message; scratch reuse across calls."""
+    from erasurehead_b200.ops import grad
+    torch.manual_seed(0)
+    rows, d = 130, 256
+    Xs = [torch.randn(rows, d, device=DEV) * 0.1 for _ in range(3)]
+    ys = [torch.where(torch.rand(rows, device=DEV) > 0.5, 1.0, -1.0) for _ in range(3)]
+    cf = [1.0, -2.5, 0.75]
+    beta = torch.randn(d, device=DEV)
+    sc = grad.dense_scratch(d, DEV)
+    want = sum(ref_grad(X, y, beta, c, 0) for X, y, c in zip(Xs, ys, cf))
+    for _ in range(3):
+        g = grad.grad_dense(Xs, ys, beta, coeff=cf, model=0, scratch=sc)
+        assert (g.double() - want).abs().max().item() <= 2e-4 * max(1.0, want.abs().max().item())
+    g2 = grad.grad_dense(Xs, ys, beta, coeff=cf, model=0, scratch=sc)
+    assert torch.equal(g, g2)            # fixed-order reduction => bitwise reproducible
+
+
+@pytest.mark.parametrize("model", [0, 1])
+def test_grad_ell_matches_reference(model):
+    from erasurehead_b200.data import generate_onehot
+    from erasurehead_b200.ops import grad
+    ds = generate_onehot(4 * 700, 5000, 19, 4, seed=1, task="linear" if model else "logistic")
+    idxs = [torch.from_numpy(ds.ell(p)).to(DEV) for p in range(2)]
+    ys = [torch.tensor(ds.labels(p), dtype=torch.float32, device=DEV) for p in range(2)]
+    beta = torch.randn(5000, device=DEV) * 0.3
+    cf = [1.0, -0.5]
+    g = grad.grad_ell(idxs, ys, beta, coeff=cf, model=model, bias_col=4999)
+    want = sum(ref_grad(torch.tensor(ds.parts[p].toarray(), device=DEV), ys[p], beta, cf[p], model) for p in range(2))
+    assert (g.double() - want).abs().max().item() <= 5e-4 * max(1.0, want.abs().max().item())
+
+
+def test_margins_loss_and_auc():
+    from erasurehead_b200.ops import metrics as mops
+    torch.manual_seed(1)
+    rows, d, R = 3000, 200, 37
+    X = torch.randn(rows, d, device=DEV)
+    Bt = torch.randn(R, d, device=DEV) * 0.1
+    y = torch.where(torch.rand(rows, device=DEV) > 0.4, 1.0, -1.0)
+    P = mops.margins_dense(X, Bt)
+    want = X.double() @ Bt.double().t()
+    assert (P.double() - want).abs().max().item() < 1e-3
+    L = mops.loss_columns(P, y, 0).cpu().numpy()
+    M = mops.loss_columns(P, y, 1).cpu().numpy()
+    Pn, yn = want.cpu().numpy(), y.cpu().numpy().astype(np.float64)
+    for c in (0, 5, R - 1):
+        assert L[c] == pytest.approx(hmetrics.logistic_loss(yn, Pn[:, c]), rel=1e-4)
+        assert M[c] == pytest.approx(hmetrics.mse(yn, Pn[:, c]), rel=1e-4)
+    s = P[:, 3].contiguous()
+    assert mops.auc(s, y).item() == pytest.approx(hmetrics.roc_auc(yn, s.cpu().numpy()), abs=1e-9)
+    st = torch.round(s * 4) / 4                     # heavy ties
+    assert mops.auc(st, y).item() == pytest.approx(hmetrics.roc_auc(yn, st.cpu().numpy()), abs=1e-9)
+
+
+def test_margins_ell():
+    from erasurehead_b200.data import generate_onehot
+    from erasurehead_b200.ops import metrics as mops
+    ds = generate_onehot(500, 900, 11, 1, seed=4)
+    idx = torch.from_numpy(ds.ell(0)).to(DEV)
+    Bt = torch.randn(9, 900, device=DEV)
+    P = mops.margins_ell(idx, Bt)
+    want = torch.tensor(ds.parts[0].toarray(), device=DEV).double() @ Bt.double().t()
+    assert (P.double() - want).abs().max().item() < 1e-4
+
+
+def test_synth_gmm_statistics_and_determinism():
+    from erasurehead_b200.ops import synth
+    rows, d = 20000, 64
+    X, y = synth.synth_gmm(rows, d, seed=7, partition=3)
+    X2, y2 = synth.synth_gmm(rows, d, seed=7, partition=3)
+    assert torch.equal(X, X2) and torch.equal(y, y2)
+    X3, _ = synth.synth_gmm(rows, d, seed=7, partition=4)
+    assert not torch.equal(X, X3)
+    assert set(y.unique().tolist()) == {-1.0, 1.0}
+    sd = X[:, :d].std().item()
+    assert sd == pytest.approx(10 / np.sqrt(d), rel=0.05)            # util.py:41 mfac
+    assert abs(X[:, :d].mean().item()) < 0.05
+    # labels carry signal: a few GD steps on the generated data beat chance
+    from erasurehead_b200.ops import grad
+    beta = torch.zeros(d, device=DEV)
+    for _ in range(30):
+        beta -= (1.0 / rows) * grad.grad_dense(X, y, beta, d=d)
+    acc = ((X[:, :d] @ beta) * y > 0).float().mean().item()
+    assert acc > 0.9
+
+
+@pytest.mark.parametrize("n,s", [(8, 2), (12, 3), (30, 3)])
+def test_codegen_matches_host(n, s):
+    from erasurehead_b200.ops import codegen
+    H = codes.parity_check(n, s, seed=2)
+    B_host = codes.cyclic_code(n, s, H=H)
+    B = codegen.cyclic_code(torch.from_numpy(H), n, s)
+    assert np.abs(B.cpu().numpy() - B_host).max() < 1e-8 * max(1.0, np.abs(B_host).max())
+    if n <= 12:
+        A = codegen.decode_table(B, s).cpu().numpy()
+        assert A.shape[0] == len(list(itertools.combinations(range(n), s)))
+        assert np.abs(A @ B_host - 1).max() < 1e-6
+        for r, missing in enumerate(itertools.combinations(range(n), s)):
+            assert np.all(A[r, list(missing)] == 0)

@@ -1,0 +1,117 @@
+"""File formats, directory layout, result files and the CLI end to end (CPU engine)."""
+import os
+
+import numpy as np
+import pytest
+from scipy.sparse import csr_matrix
+
+from erasurehead_b200 import cli
+from erasurehead_b200.config import parse_argv
+from erasurehead_b200.data import generate_gmm, generate_gmm_to_disk, generate_onehot, load_dataset
+from erasurehead_b200.data.dataset import csr_to_ell, ell_to_csr
+from erasurehead_b200.utils import io, metrics
+
+
+def test_vector_and_matrix_formats(tmp_path):
+    p = str(tmp_path / "v.dat")
+    io.save_vector([1.0, -1.0, 0.12345], p)
+    assert open(p).read() == "1.000 \n-1.000 \n0.123 \n"          # util.py:32-36 "%5.3f" + " "
+    m = np.array([[1.5, -2.25], [3.0, 4.0]])
+    q = str(tmp_path / "m.dat")
+    io.save_matrix(m, q)
+    assert open(q).read().splitlines()[0] == "1.5 -2.25"          # util.py:26-30 str(float)
+    assert np.array_equal(io.load_data(q), m)
+    s = csr_matrix(np.array([[0, 1.0, 0], [1.0, 0, 1.0]]))
+    io.save_sparse_csr(str(tmp_path / "s"), s)
+    z = np.load(str(tmp_path / "s.npz"))
+    assert set(z.files) == {"data", "indices", "indptr", "shape"}  # util.py:17-19
+    assert (io.load_sparse_csr(str(tmp_path / "s")) != s).nnz == 0
+
+
+def test_auc_matches_sklearn():
+    from sklearn.metrics import auc, roc_curve
+    rng = np.random.RandomState(0)
+    for ties in (False, True):
+        y = rng.choice([-1.0, 1.0], 500)
+        s = rng.randn(500) + 0.5 * y
+        if ties:
+            s = np.round(s, 1)
+        fpr, tpr, _ = roc_curve(y, s, pos_label=1)
+        assert metrics.roc_auc(y, s) == pytest.approx(auc(fpr, tpr), abs=1e-12)
+    assert metrics.logistic_loss([1, -1], [0.0, 0.0]) == pytest.approx(np.log(2))
+    assert metrics.mse([1, 2], [1, 4]) == 2.0
+
+
+def test_generate_to_disk_layout_and_reload(tmp_path):
+    out = generate_gmm_to_disk(5, 400, 6, str(tmp_path), 1, 0, 0, seed=1)
+    assert out.endswith("artificial-data/400x6/4/")                # generate_data.py:59-60
+    assert sorted(os.listdir(out)) == ["1.dat", "2.dat", "3.dat", "4.dat", "label.dat", "label_test.dat",
+                                       "test_data.dat"]
+    ds = load_dataset(out, 4, False, 6)
+    assert ds.parts[0].shape == (100, 6) and ds.X_test.shape == (80, 6) and set(np.unique(ds.y)) <= {-1.0, 1.0}
+    out = generate_gmm_to_disk(5, 480, 6, str(tmp_path), 1, 4, 1, seed=1)
+    assert out.endswith("artificial-data/480x6/partial/12/")       # generate_data.py:61-62
+
+
+def test_onehot_shapes_and_ell_roundtrip():
+    ds = generate_onehot(600, 500, 9, 4, seed=2)
+    assert ds.is_sparse and ds.parts[0].shape == (150, 500)
+    idx = ds.ell(0)
+    assert idx.shape == (150, 9) and np.all(idx[:, -1] == 499)      # bias column is always on
+    assert (ell_to_csr(idx, 500) != ds.parts[0]).nnz == 0
+    assert np.array_equal(csr_to_ell(ds.parts[1]), ds.ell(1))
+
+
+@pytest.mark.parametrize("scheme_args,prefix,files", [
+    ("1 1 0 3 5 1 AGD", "approx_acc_1_5", ["training_loss", "testing_loss", "auc", "timeset", "worker_timeset"]),
+    ("1 2 0 0 0 1 GD", "coded_acc_2", ["training_loss", "auc"]),
+    ("0 0 0 1 0 1 GD", "naive_acc", ["timeset"]),
+])
+def test_cli_end_to_end_dense(tmp_path, capsys, scheme_args, prefix, files):
+    generate_gmm_to_disk(9, 800, 6, str(tmp_path), 1, 0, 0, seed=1)
+    argv = f"9 800 6 {tmp_path} 0 x {scheme_args} --rounds=6 --gpus=-1".split()
+    out = cli.run(parse_argv(argv))
+    res_dir = out["results_dir"]
+    assert res_dir == f"{tmp_path}/artificial-data/800x6/8/results/"     # naive.py:200-202
+    for f in files:
+        assert os.path.exists(f"{res_dir}{prefix}_{f}.dat"), f
+    assert np.load(f"{res_dir}{prefix}_betaset.npy").shape == (6, 6)
+    wt = io.load_data(f"{res_dir}{prefix}_worker_timeset.dat")
+    assert wt.shape == (6, 8)
+    txt = capsys.readouterr().out
+    assert "Iteration 5: Train Loss =" in txt and "AUC =" in txt and "Total Time Elapsed:" in txt
+    assert ">>> At Iteration 0" in txt
+
+
+def test_cli_sparse_partial_and_compat_names(tmp_path):
+    n, s, P = 4, 1, 3
+    ds = generate_onehot(8 * 50, 120, 7, (P - s) * n, seed=3)
+    d = f"{tmp_path}/amazon-dataset/partial/{(P - s) * n}/"
+    ds.save(d)
+    argv = f"5 400 120 {tmp_path} 1 amazon-dataset 1 {s} {P} 0 0 0 AGD --rounds=4 --gpus=-1 --compat".split()
+    out = cli.run(parse_argv(argv))
+    rd = out["results_dir"]
+    assert rd == d + "results/"
+    # Q3: partial_coded writes training loss under the partialreplication_ prefix in compat mode
+    assert os.path.exists(rd + f"partialreplication_{s}_{P}_training_loss.dat")
+    assert os.path.exists(rd + f"partialcoded_{s}_{P}_testing_loss.dat")
+
+
+def test_checkpoint_resume_cpu(tmp_path):
+    generate_gmm_to_disk(9, 800, 6, str(tmp_path), 1, 0, 0, seed=1)
+    base = f"9 800 6 {tmp_path} 0 x 1 1 0 3 5 1 AGD --gpus=-1 --quiet"
+    full = cli.run(parse_argv((base + " --rounds=8").split()))["result"]
+    half = cli.run(parse_argv((base + " --rounds=4").split()))
+    from erasurehead_b200 import Engine
+    from erasurehead_b200.data import load_dataset as ld
+    cfg = parse_argv((base + " --rounds=4").split())
+    eng = Engine(cfg, ld(cfg.data_dir, 8, False, 6), device="cpu")
+    eng.run()
+    ck = str(tmp_path / "ck.npz")
+    eng.save_checkpoint(ck, 4)
+    cfg2 = parse_argv((base + f" --rounds=8 --resume={ck}").split())
+    eng2 = Engine(cfg2, ld(cfg2.data_dir, 8, False, 6), device="cpu")
+    assert eng2.first_round == 4
+    res2 = eng2.run()
+    assert np.allclose(res2.betaset, full.betaset[4:], atol=1e-12)
+    assert np.allclose(res2.timeset, full.timeset[4:])
