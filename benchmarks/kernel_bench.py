@@ -1,0 +1,119 @@
+#!/usr/bin/env python
+"""Kernel-level timings against the measured roofline (MEASURED_PEAKS.json).
+
+    python benchmarks/kernel_bench.py [--rows R --cols D --iters I] [--only grad|decoder|eval]
+
+Each kernel is timed with CUDA events after warm-up; inputs are larger than L2 (or L2 is
+flushed between iterations for the small ones).  Prints one JSON line per kernel.
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+
+def peaks():
+    p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "MEASURED_PEAKS.json")
+    try:
+        return json.load(open(p)), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+def time_fn(fn, iters, warmup=3, flush=None):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.median(ts)), float(np.min(ts))
+
+
+def bench_grad(args, pk, src):
+    from erasurehead_b200.ops import grad, synth
+    out = []
+    for d in args.cols:
+        rows = args.rows if args.rows else max(4096, int(6e9 // (4 * d)))
+        X, y = synth.synth_gmm(rows, d, 1, 0)
+        beta = torch.randn(d, device="cuda") * 0.01
+        sc = grad.dense_scratch(X.stride(0), "cuda")
+        o = torch.empty(d, device="cuda")
+        med, mn = time_fn(lambda: grad.grad_dense(X, y, beta, d=d, scratch=sc, out=o), args.iters)
+        byt = rows * X.stride(0) * 4
+        # torch two-pass baseline (two cuBLAS GEMVs + elementwise)
+        def two_pass():
+            p = X[:, :d] @ beta
+            r = -y / (torch.exp(p * y) + 1)
+            return X[:, :d].t() @ r
+        med2, _ = time_fn(two_pass, max(3, args.iters // 2))
+        rec = {"kernel": "grad_dense", "rows": rows, "d": d, "ms": med, "ms_min": mn, "GBps": byt / med / 1e6,
+               "frac_of_hbm_" + src: byt / med / 1e6 / pk["hbm_gbs"], "torch_two_pass_ms": med2,
+               "speedup_vs_two_pass": med2 / med}
+        print(json.dumps(rec)); out.append(rec)
+        del X, y
+    return out
+
+
+def bench_decoder(args):
+    """Latency of a full round with zero delay and a tiny problem (launch + flags + decode)."""
+    from erasurehead_b200 import Engine, RunConfig, triple_from_scheme
+    out = []
+    for scheme, s in (("approx", 1), ("coded", 2), ("naive", 0)):
+        ic, pp, cv = triple_from_scheme(scheme)
+        cfg = RunConfig(9, 8 * 256, 4096, "", 0, "x", ic, s, pp, cv, 4, 0, "AGD", rounds=220, synthetic=True, seed=1)
+        eng = Engine(cfg, None)
+        eng.prepare(); eng.enqueue(20); eng.finish()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); eng.enqueue(200); e1.record(); eng.finish()
+        us = e0.elapsed_time(e1) / 200 * 1e3
+        dec = float(eng.t_timeset[20:220].mean().item()) * 1e6
+        rec = {"kernel": "round_latency", "scheme": scheme, "n_workers": 8, "d": 4096, "us_per_round": us,
+               "kernels_per_round": eng.launches_per_round(), "decoder_timeset_us": dec}
+        print(json.dumps(rec)); out.append(rec)
+        eng.close()
+    return out
+
+
+def bench_eval(args, pk, src):
+    from erasurehead_b200.ops import metrics as mops, synth
+    rows, d, R = 262144, 4096, 100
+    X, y = synth.synth_gmm(rows, d, 1, 0)
+    Bt = torch.randn(R, d, device="cuda") * 0.01
+    med, _ = time_fn(lambda: mops.margins_dense(X, Bt, d), 5)
+    med2, _ = time_fn(lambda: X @ Bt.t(), 5)
+    fl = 2.0 * rows * d * R
+    rec = {"kernel": "margins_dense", "rows": rows, "d": d, "R": R, "ms": med, "TFLOPs": fl / med / 1e9,
+           "cublas_fp32_ms": med2}
+    print(json.dumps(rec))
+    return [rec]
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=0)
+    ap.add_argument("--cols", type=int, nargs="+", default=[4096, 1024, 2048, 8192, 512])
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--only", default="")
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    pk, src = peaks()
+    recs = []
+    if args.only in ("", "grad"):
+        recs += bench_grad(args, pk, src)
+    if args.only in ("", "decoder"):
+        recs += bench_decoder(args)
+    if args.only in ("", "eval"):
+        recs += bench_eval(args, pk, src)
+    if args.out:
+        json.dump(recs, open(args.out, "w"), indent=1)

@@ -76,8 +76,8 @@ def test_engine_solve_decode_equals_table():
 
 def test_engine_sparse_linear_and_logistic():
     for task, model in (("logistic", None), ("linear", "linear")):
-        cfg = mk("approx", s=1, k=6, rows=8 * 120, d=700, model=model, eta0=(0.05 if model else 10.0), is_real=1)
-        cfg.dataset = "amazon-dataset"
+        cfg = mk("approx", s=1, k=6, rows=8 * 120, d=700, model=model, eta0=(0.05 if model else 10.0))
+        cfg.is_real, cfg.dataset = 1, "amazon-dataset"
         data = generate_onehot(cfg.n_rows, cfg.n_cols, 13, 8, seed=2, task=task)
         dl = spaced_delays(cfg.rounds, 8, seed=1)
         eng = Engine(cfg, data, delays=dl)
