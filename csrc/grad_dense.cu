@@ -374,3 +374,60 @@ extern "C" int eh_grad_dense(const eh_grad_job* j, void* d_scratch, size_t scrat
     if (j->ld <= 4096) return launch<4, 4>(j, p, d_scratch, scratch_bytes, st);
     return launch<8, 2>(j, p, d_scratch, scratch_bytes, st);
 }
+
+// ------------------------------------------------------------------------------------------
+// eh_grad_dense_noalloc: the same fused gradient kernel for callers that cannot allocate.
+//
+// Who that is: a host that drives this library from a fixed-latency loop where cudaMalloc (and
+// the device-wide synchronisation it implies) is forbidden after start-up; a process whose HBM
+// is already fully committed to resident partitions so that a late allocation may simply fail;
+// or a plain C caller that was handed device pointers for inputs and outputs but owns no
+// allocator of its own.  Such callers still pass inputs and outputs; only the scratch (the
+// per-CTA partial gradients and the three barrier words) is provided here, in a file-scope
+// device array that every GPU loading this library holds until the process exits.
+//
+// Limits: row stride ld <= EH_NOALLOC_MAX_LD floats and at most EH_NOALLOC_MAX_CTAS
+// cooperative CTAs (one per SM), i.e. 512 B + 160 * 4096 * 4 B = 2.5 MiB per GPU.  Larger
+// problems are rejected with EH_EINVAL and a message; use eh_grad_dense with your own scratch.
+//
+// Set-up: the first call on each device resolves the array's device address with
+// cudaGetSymbolAddress (in host code the array's name is only a host-side stand-in, not a device
+// address) and caches it per device.  Make that first call before any stream capture begins.
+// Every call shares the one array, which still holds the previous call's partials: the barrier
+// words that must start at zero are cleared on the caller's stream before each launch, the
+// partials are fully overwritten before they are read.  Two calls that overlap on the GPU
+// (different streams, or different host threads on the same device) race on the array -- keep
+// calls on one device stream-ordered.
+// ------------------------------------------------------------------------------------------
+#define EH_NOALLOC_MAX_LD   4096
+#define EH_NOALLOC_MAX_CTAS 160
+#define EH_NOALLOC_BYTES    (sizeof(eh::GradScratchHdr) + (size_t)EH_NOALLOC_MAX_CTAS * EH_NOALLOC_MAX_LD * sizeof(float))
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[EH_NOALLOC_BYTES];
+
+extern "C" size_t eh_grad_dense_noalloc_max_ld(void) { return EH_NOALLOC_MAX_LD; }
+
+extern "C" int eh_grad_dense_noalloc(const eh_grad_job* j, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(j, "grad_dense_noalloc: null job");
+    EH_REQUIRE(j->ld <= EH_NOALLOC_MAX_LD,
+               "grad_dense_noalloc: row stride ld=%d exceeds the built-in scratch limit of %d floats; "
+               "call eh_grad_dense with caller-provided scratch instead", j->ld, EH_NOALLOC_MAX_LD);
+    const DevInfo& di = dev_info();
+    EH_REQUIRE(di.device >= 0 && di.device < 64, "grad_dense_noalloc: no current CUDA device");
+    EH_REQUIRE(di.sm_count <= EH_NOALLOC_MAX_CTAS,
+               "grad_dense_noalloc: device has %d SMs, built-in scratch is sized for %d CTAs", di.sm_count,
+               EH_NOALLOC_MAX_CTAS);
+    // once per device, with that device current: device address of the file-scope array
+    static void* dev_ptr[64] = {nullptr};
+    if (dev_ptr[di.device] == nullptr) {
+        void* p = nullptr;
+        EH_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        EH_REQUIRE(p != nullptr, "grad_dense_noalloc: cudaGetSymbolAddress returned a null address");
+        dev_ptr[di.device] = p;
+    }
+    void* scratch = dev_ptr[di.device];
+    // the array keeps the last call's contents: zero the barrier/decision words, stream-ordered
+    EH_CUDA(cudaMemsetAsync(scratch, 0, sizeof(GradScratchHdr), (cudaStream_t)stream));
+    return eh_grad_dense(j, scratch, EH_NOALLOC_BYTES, stream);
+}

@@ -118,6 +118,8 @@ def _declare(lib):
         "eh_ws_error": (i32, [P(WsLayout), vp, P(i32), vp]),
         "eh_grad_dense_scratch_bytes": (sz, [i32]),
         "eh_grad_dense": (i32, [P(GradJob), vp, sz, vp]),
+        "eh_grad_dense_noalloc_max_ld": (sz, []),
+        "eh_grad_dense_noalloc": (i32, [P(GradJob), vp]),
         "eh_grad_ell_scratch_bytes": (sz, [i32]),
         "eh_grad_ell": (i32, [P(GradEllJob), vp, sz, vp]),
         "eh_decoder_scratch_bytes": (sz, []),

@@ -104,6 +104,17 @@ typedef struct eh_grad_job {
 size_t eh_grad_dense_scratch_bytes(int d);
 int eh_grad_dense(const eh_grad_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
 
+/* Same kernel for callers that cannot allocate device memory (fixed-latency loops that forbid
+ * cudaMalloc after start-up, processes whose HBM is fully committed, plain C hosts without an
+ * allocator): the scratch lives in a file-scope device array inside the library (2.5 MiB per
+ * GPU, held until exit).  No counterpart in the reference.  Limits: ld <= 4096 floats
+ * (eh_grad_dense_noalloc_max_ld()), devices with <= 160 SMs; larger shapes return EH_EINVAL.
+ * The first call on each device resolves the array's address (make it before any stream
+ * capture); calls sharing a device must be stream-ordered -- overlapping calls race on the array.
+ * Calls no cudaMalloc/cudaFree and no allocating library routine. */
+size_t eh_grad_dense_noalloc_max_ld(void);
+int eh_grad_dense_noalloc(const eh_grad_job* job, void* stream);
+
 /* One-hot ELL features (every value 1.0; arrange_real_data.py:41-64): gather-sum margins,
  * scatter-add gradient with the always-on bias column reduced in registers. */
 typedef struct eh_grad_ell_job {
