@@ -1,0 +1,55 @@
+"""World-size > 1: gloo on CPU for the host-side logic, NCCL + peer-mapped memory on GPUs."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ALL = ["naive", "coded", "replication", "avoidstragg", "approx", "partial_coded", "partial_replication", "sparse"]
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _torchrun(nproc, device, schemes, timeout=300):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(HERE, "mp_engine_check.py"), device] + schemes
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
+    return p.returncode, p.stdout + p.stderr
+
+
+def test_two_process_gloo_cpu():
+    rc, out = _torchrun(2, "cpu", ["approx", "coded", "partial_coded"])
+    assert rc == 0, out[-3000:]
+    assert out.count("OK") == 3
+
+
+def _gpu_count():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(_gpu_count() < 2, reason="needs >= 2 GPUs")
+def test_two_gpu_peer_path_all_schemes():
+    rc, out = _torchrun(2, "cuda", ALL)
+    assert rc == 0, out[-3000:]
+    assert out.count("OK") == len(ALL)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(_gpu_count() < 8, reason="needs 8 GPUs")
+def test_eight_gpu_peer_path_all_schemes():
+    rc, out = _torchrun(8, "cuda", ALL)
+    assert rc == 0, out[-3000:]
+    assert out.count("OK") == len(ALL)
