@@ -96,7 +96,17 @@ def bench_eval(args, pk, src):
     rec = {"kernel": "margins_dense", "rows": rows, "d": d, "R": R, "ms": med, "TFLOPs": fl / med / 1e9,
            "cublas_fp32_ms": med2}
     print(json.dumps(rec))
-    return [rec]
+    torch.backends.cuda.matmul.allow_tf32 = True
+    med3, _ = time_fn(lambda: X @ Bt.t(), 5)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ls = torch.zeros(R, dtype=torch.float64, device="cuda")
+    medt, mint = time_fn(lambda: mops.eval_tc(X, Bt, y, kind=0, d=d, loss_sums=ls), 10)
+    byt = rows * X.stride(0) * 4
+    rec2 = {"kernel": "eval_tc(tcgen05 tf32 + fused loss)", "rows": rows, "d": d, "R": R, "ms": medt, "ms_min": mint,
+            "TFLOPs": fl / medt / 1e9, "GBps": byt / medt / 1e6, "frac_of_hbm_" + src: byt / medt / 1e6 / pk["hbm_gbs"],
+            "cublas_tf32_gemm_only_ms": med3, "cublas_fp32_gemm_only_ms": med2}
+    print(json.dumps(rec2))
+    return [rec, rec2]
 
 
 if __name__ == "__main__":

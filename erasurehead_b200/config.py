@@ -98,6 +98,7 @@ class RunConfig:
     checkpoint_every: int = 0
     resume: Optional[str] = None
     eval: str = "full"                     # full | none
+    eval_precision: str = "tf32"           # tf32 (tcgen05 tensor cores) | fp32 (CUDA cores)
     metrics_jsonl: Optional[str] = None
     decode: str = "auto"                   # auto | table | solve
     quiet: bool = False

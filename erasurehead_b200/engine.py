@@ -343,16 +343,26 @@ class Engine:
         n_parts = spec.n_partitions - (1 if cfg.compat and spec.n_partitions > 1 else 0)   # Q1
         tr = torch.zeros(R, dtype=torch.float64, device=dev)
         rows = 0
+        # dense data: one tcgen05/TMEM pass over X evaluates all R iterates with the loss fused in
+        # the epilogue (csrc/eval_tc.cu); --eval-precision=fp32 selects the exact CUDA-core path
+        use_tc = (not self.sparse) and cfg.eval_precision == "tf32"
         for p in range(n_parts):
             Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
-            P = mops.margins_ell(Xp, Bt) if self.sparse else mops.margins_dense(Xp, Bt, d)
-            tr += mops.loss_columns(P, yp, kind) * Xp.shape[0]
+            if use_tc:
+                mops.eval_tc(Xp, Bt, yp, kind=kind, d=d, loss_sums=tr)
+            else:
+                P = mops.margins_ell(Xp, Bt) if self.sparse else mops.margins_dense(Xp, Bt, d)
+                tr += mops.loss_columns(P, yp, kind) * Xp.shape[0]
+                del P
             rows += Xp.shape[0]
-            del P
         tr /= rows
         Xt, yt = self._device_test()
-        Pt = mops.margins_ell(Xt, Bt) if self.sparse else mops.margins_dense(Xt, Bt, d)
-        te = mops.loss_columns(Pt, yt, kind)
+        if use_tc:
+            te, Pt = mops.eval_tc(Xt, Bt, yt, kind=kind, d=d, want_margins=True)
+            te = te / Xt.shape[0]
+        else:
+            Pt = mops.margins_ell(Xt, Bt) if self.sparse else mops.margins_dense(Xt, Bt, d)
+            te = mops.loss_columns(Pt, yt, kind)
         auc = None
         if self.model.has_auc:
             Pcol = Pt.t().contiguous()

@@ -128,6 +128,7 @@ def _declare(lib):
         "eh_run_rounds": (i32, [P(RoundPlan), i32, i32, i32, vp]),
         "eh_margins_dense": (i32, [vp, i64, i32, i32, vp, i32, i32, vp, vp]),
         "eh_margins_ell": (i32, [vp, i64, i32, vp, i32, i32, vp, vp]),
+        "eh_eval_tc": (i32, [vp, i64, i32, i32, vp, i32, i32, vp, i32, vp, vp, i32, vp]),
         "eh_loss_columns": (i32, [vp, vp, i64, i32, i32, vp, vp]),
         "eh_auc": (i32, [vp, vp, i64, vp, vp, sz, vp]),
         "eh_auc_scratch_bytes": (sz, [i64]),

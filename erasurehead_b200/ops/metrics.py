@@ -46,3 +46,22 @@ def auc(scores: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
     check(lib().eh_auc(scores.data_ptr(), labels.data_ptr(), n, out.data_ptr(), scratch.data_ptr(), nbytes,
                        stream_ptr()), "eh_auc")
     return out
+
+
+def eval_tc(X: torch.Tensor, Bt: torch.Tensor, y: torch.Tensor | None = None, kind: int = 0, d: int | None = None,
+            want_margins: bool = False, loss_sums: torch.Tensor | None = None):
+    """tcgen05/TMEM evaluation: one pass over ``X`` for all ``R`` iterates (TF32 operands).
+
+    Returns ``(loss_sums[R] float64 or None, P[rows, R] float32 or None)``.  ``loss_sums`` holds
+    column SUMS (accumulates into the tensor passed in, so partitions can be chained)."""
+    assert X.dtype == torch.float32 and Bt.dtype == torch.float32 and X.stride(1) == 1 and Bt.stride(1) == 1
+    d = int(d or Bt.shape[1])
+    R = Bt.shape[0]
+    if y is not None and loss_sums is None:
+        loss_sums = torch.zeros(R, dtype=torch.float64, device=X.device)
+    P = torch.empty((X.shape[0], R), dtype=torch.float32, device=X.device) if want_margins else None
+    check(lib().eh_eval_tc(X.data_ptr(), X.shape[0], d, X.stride(0), Bt.data_ptr(), R, Bt.stride(0),
+                           0 if y is None else y.data_ptr(), int(kind),
+                           0 if (y is None or loss_sums is None) else loss_sums.data_ptr(),
+                           0 if P is None else P.data_ptr(), R, stream_ptr()), "eh_eval_tc")
+    return (loss_sums if y is not None else None), P

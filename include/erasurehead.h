@@ -227,6 +227,13 @@ int eh_margins_dense(const float* d_X, int64_t rows, int d, int ld, const float*
                      int ldb, float* d_P, void* stream);
 int eh_margins_ell(const int32_t* d_idx, int64_t rows, int nnz, const float* d_Bt, int R, int ldb,
                    float* d_P, void* stream);
+/* Tensor-core version (tcgen05.mma kind::tf32, TMEM accumulators, TMA tensor-map loads): one pass
+ * over X evaluates all R iterates; d_loss_sums[R] (zeroed by the caller) receives the per-column
+ * SUM of log(1+exp(-y p)) (kind 0) or (y-p)^2 (kind 1); d_P (optional, [rows, ldp]) receives the
+ * margins.  X and Bt rows must be zero-padded to a multiple of 32 floats (ld, ldb >= that).
+ * Reference: the per-iterate evaluation loop naive.py:186-198 + util.py:136-141. */
+int eh_eval_tc(const float* d_X, int64_t rows, int d, int ld, const float* d_Bt, int R, int ldb,
+               const float* d_y, int kind, double* d_loss_sums, float* d_P, int ldp, void* stream);
 /* column-wise loss of P[rows, R] against y: kind 0 = logistic, 1 = squared error; out[R] = sum.
  * d_out must be zeroed by the caller; accumulation is in double. */
 int eh_loss_columns(const float* d_P, const float* d_y, int64_t rows, int R, int kind,

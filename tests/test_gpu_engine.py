@@ -55,9 +55,14 @@ def test_engine_matches_oracle(scheme, kw, rule):
     ev = eng.evaluate(res)
     from erasurehead_b200 import results
     evh = results.evaluate_host(eng.model, data, res.betaset)
-    assert np.allclose(ev.training_loss, evh.training_loss, rtol=2e-4, atol=1e-5)
-    assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=2e-4, atol=1e-5)
-    assert np.allclose(ev.auc, evh.auc, atol=2e-3)
+    # default evaluation runs on the tensor cores with TF32 operands
+    assert np.allclose(ev.training_loss, evh.training_loss, rtol=2e-3, atol=1e-4)
+    assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=2e-3, atol=1e-4)
+    assert np.allclose(ev.auc, evh.auc, atol=3e-3)
+    eng.cfg.eval_precision = "fp32"
+    ev32 = eng.evaluate(res)
+    assert np.allclose(ev32.training_loss, evh.training_loss, rtol=2e-4, atol=1e-5)
+    assert np.allclose(ev32.auc, evh.auc, atol=2e-3)
     eng.close()
 
 

@@ -135,3 +135,29 @@ def test_codegen_matches_host(n, s):
         assert np.abs(A @ B_host - 1).max() < 1e-6
         for r, missing in enumerate(itertools.combinations(range(n), s)):
             assert np.all(A[r, list(missing)] == 0)
+
+
+@pytest.mark.parametrize("rows,d,R", [(128, 32, 16), (1000, 200, 37), (5000, 4096, 100), (777, 96, 150)])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_eval_tc_tensor_core_margins_and_loss(rows, d, R, kind):
+    """tcgen05/TMEM evaluation vs the fp64 reference (TF32 operands: ~1e-3 relative on margins)."""
+    from erasurehead_b200.ops import metrics as mops, synth
+    torch.manual_seed(rows + R)
+    ld = synth.pad_cols(d)
+    X = torch.zeros(rows, ld, device=DEV)
+    X[:, :d] = torch.randn(rows, d, device=DEV)
+    Bt = torch.zeros(R, ld, device=DEV)
+    Bt[:, :d] = torch.randn(R, d, device=DEV) / np.sqrt(d)
+    y = torch.where(torch.rand(rows, device=DEV) > 0.4, 1.0, -1.0) if kind == 0 else torch.randn(rows, device=DEV)
+    sums, P = mops.eval_tc(X, Bt, y, kind=kind, d=d, want_margins=True)
+    want = X[:, :d].double() @ Bt[:, :d].double().t()
+    assert (P.double() - want).abs().max().item() < 8e-3
+    if kind == 0:
+        ref = torch.nn.functional.softplus(-y.double()[:, None] * want).sum(0)
+    else:
+        ref = ((y.double()[:, None] - want) ** 2).sum(0)
+    rel = ((sums - ref).abs() / ref.abs().clamp_min(1e-9)).max().item()
+    assert rel < 2e-3, rel
+    # loss-only call (no margins written) gives the same sums
+    sums2, P2 = mops.eval_tc(X, Bt, y, kind=kind, d=d)
+    assert P2 is None and torch.allclose(sums, sums2, rtol=1e-12)
