@@ -23,7 +23,7 @@ from .models import Model, get_model
 from .schemes import (DECODE_FIRST_PER_GROUP, DECODE_LSTSQ, DECODE_SUM, MSG_CODED, MSG_PRIVATE,
                       SchemeSpec)
 
-__all__ = ["RunResult", "gd_update", "agd_update", "worker_messages", "run_rounds", "initial_beta"]
+__all__ = ["RunResult", "gd_update", "agd_update", "worker_messages", "plan_round", "run_rounds", "initial_beta"]
 
 
 @dataclass
@@ -79,6 +79,60 @@ def worker_messages(model: Model, spec: SchemeSpec, data, w: int, beta: np.ndarr
     return out
 
 
+def plan_round(spec: SchemeSpec, delay_row: np.ndarray, compute_time: float = 0.0, round_index: int = 0):
+    """Replay the master's Waitany loop for one round given only the message delays.
+
+    Returns ``(a, priv, t_stop, n_coded, worker_time)``: decode weights of the coded messages,
+    0/1 weights of the private messages, the time the stop rule fired, the number of coded
+    messages consumed and the per-worker arrival time (-1 if the coded message was not
+    collected).  Pure function of the scheme and the delay row -- shared by the oracle and the
+    NCCL baseline (which has no device-side arrival detection)."""
+    n = spec.n
+    has_priv = spec.n_msgs > 1
+    events = []
+    for w in range(n):
+        dl = delay_row[w]
+        if has_priv:
+            events.append((compute_time + dl, 0, w, MSG_PRIVATE))
+        events.append(((2 * compute_time if has_priv else compute_time) + dl, 1, w, MSG_CODED))
+    events.sort()
+    done = np.zeros(n, dtype=bool)
+    priv = np.zeros(n)
+    grp_cov = np.zeros(spec.n_groups, dtype=bool)
+    first_of_group = np.zeros(n, dtype=bool)
+    n_priv = n_coded = 0
+    t_last = 0.0
+    seen_t = np.full(n, -1.0)
+    for (t, _, w, kind) in events:
+        if spec.stop(n_priv, n_coded, int(grp_cov.sum())):
+            break
+        if not np.isfinite(t):
+            raise RuntimeError(
+                f"round {round_index}: stop rule cannot be met, too many dead workers for scheme {spec.name}")
+        t_last = t
+        seen_t[w] = t
+        if kind == MSG_PRIVATE:
+            priv[w] = 1.0
+            n_priv += 1
+            continue
+        n_coded += 1
+        done[w] = True
+        gid = spec.group_of[w]
+        if not grp_cov[gid]:
+            grp_cov[gid] = True
+            first_of_group[w] = True
+    if not spec.stop(n_priv, n_coded, int(grp_cov.sum())):
+        raise RuntimeError(f"round {round_index}: stop rule not met after all arrivals")
+    if spec.decode == DECODE_SUM:
+        a = done.astype(np.float64)
+    elif spec.decode == DECODE_FIRST_PER_GROUP:
+        a = first_of_group.astype(np.float64)
+    else:
+        a = codes.decode_weights(spec.B, done)                             # coded.py:147-149
+    wt = np.where(done, seen_t, -1.0)                                      # -1 for the uncollected
+    return a, priv, t_last, n_coded, wt
+
+
 def run_rounds(cfg, spec: SchemeSpec, data, delays: np.ndarray, beta0: Optional[np.ndarray] = None,
                u0: Optional[np.ndarray] = None, first_round: int = 0, rounds: Optional[int] = None,
                compute_time: float = 0.0, model: Optional[Model] = None) -> RunResult:
@@ -100,53 +154,15 @@ def run_rounds(cfg, spec: SchemeSpec, data, delays: np.ndarray, beta0: Optional[
     for r in range(R):
         i = first_round + r
         msgs = [worker_messages(model, spec, data, w, beta) for w in range(n)]
-        events = []
-        for w in range(n):
-            dl = delays[r, w]
-            if MSG_PRIVATE in msgs[w]:
-                events.append((compute_time + dl, 0, w, MSG_PRIVATE))
-            events.append((2 * compute_time + dl if MSG_PRIVATE in msgs[w] else compute_time + dl,
-                           1, w, MSG_CODED))
-        events.sort()
+        a, priv, t_last, n_coded, wt = plan_round(spec, delays[r], compute_time, i)
         g = np.zeros_like(beta)
-        done = np.zeros(n, dtype=bool)
-        grp_cov = np.zeros(spec.n_groups, dtype=bool)
-        first_of_group = np.zeros(n, dtype=bool)
-        n_priv = n_coded = 0
-        t_last = 0.0
-        wts[r, :] = -1.0
-        seen_t = np.full(n, -1.0)
-        for (t, _, w, kind) in events:
-            if spec.stop(n_priv, n_coded, int(grp_cov.sum())):
-                break
-            if not np.isfinite(t):
-                raise RuntimeError(
-                    f"round {i}: stop rule cannot be met, too many dead workers for scheme {spec.name}")
-            t_last = t
-            seen_t[w] = t
-            if kind == MSG_PRIVATE:
-                g += msgs[w][MSG_PRIVATE]
-                n_priv += 1
-                continue
-            n_coded += 1
-            done[w] = True
-            gid = spec.group_of[w]
-            if not grp_cov[gid]:
-                grp_cov[gid] = True
-                first_of_group[w] = True
-        if not spec.stop(n_priv, n_coded, int(grp_cov.sum())):
-            raise RuntimeError(f"round {i}: stop rule not met after all arrivals")
-        if spec.decode == DECODE_SUM:
-            a = done.astype(np.float64)
-        elif spec.decode == DECODE_FIRST_PER_GROUP:
-            a = first_of_group.astype(np.float64)
-        else:
-            a = codes.decode_weights(spec.B, done)                         # coded.py:147-149
+        for w in np.flatnonzero(priv):
+            g += msgs[w][MSG_PRIVATE]
         for w in np.flatnonzero(a):
             g += a[w] * msgs[w][MSG_CODED]
         weights[r] = a
         ncol[r] = n_coded
-        wts[r, done] = seen_t[done]                                        # -1 for the uncollected
+        wts[r] = wt
 
         gm = eta[i] * spec.lr_scale / N
         if cfg.update_rule == "GD":

@@ -131,3 +131,15 @@ def test_synthetic_on_device_and_checkpoint_resume(tmp_path):
     r2 = second.run()
     assert np.allclose(r2.betaset, rf.betaset[4:], atol=1e-6)
     second.close()
+
+
+def test_nccl_baseline_engine_matches_oracle_single_gpu():
+    """Baseline B2 (torch + cuBLAS, library calls only) follows the same trajectory."""
+    from erasurehead_b200.parallel.nccl_baseline import NcclBaselineEngine
+    cfg = mk("coded", s=2, seed=3, rounds=4)
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1)
+    dl = spaced_delays(cfg.rounds, 8, seed=5, gap=1e-4)
+    eng = NcclBaselineEngine(cfg, data, delays=dl)
+    eng.prepare(); eng.enqueue(4); eng.finish()
+    ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl)
+    assert np.abs(eng.beta.cpu().numpy() - ref.betaset[-1]).max() <= 5e-4 * max(1.0, np.abs(ref.betaset).max())
