@@ -70,3 +70,22 @@ def generate_gmm_to_disk(n_procs: int, n_rows: int, n_cols: int, output_dir: str
         out = f"{base}partial/{parts}/"
     generate_gmm(n_rows, n_cols, parts, seed=seed).save(out)
     return out
+
+
+def main(argv=None) -> int:
+    """CLI with the seven positionals of ``generate_data.py:50-52``."""
+    import sys
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if len(argv) != 7:
+        print("Usage: python -m erasurehead_b200.data.generate n_procs n_rows n_cols output_dir n_stragglers "
+              "n_partitions partial_coded")
+        return 0
+    n_procs, n_rows, n_cols, out, s, P, partial = argv
+    path = generate_gmm_to_disk(int(n_procs), int(n_rows), int(n_cols), out, int(s), int(P), int(partial))
+    print("Data Generation Finished.", path)
+    return 0
+
+
+if __name__ == "__main__":
+    import sys
+    sys.exit(main())

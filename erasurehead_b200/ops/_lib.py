@@ -133,6 +133,8 @@ def _declare(lib):
         "eh_auc": (i32, [vp, vp, i64, vp, vp, sz, vp]),
         "eh_auc_scratch_bytes": (sz, [i64]),
         "eh_synth_gmm": (i32, [vp, vp, i64, i32, i32, u64, u64, i32, vp]),
+        "eh_onehot_assemble": (i32, [vp, vp, i64, i32, vp, vp]),
+        "eh_pair_codes": (i32, [vp, i64, i32, vp, i32, vp, vp, vp]),
         "eh_code_cyclic": (i32, [vp, i32, i32, vp, vp]),
         "eh_code_decode_table": (i32, [vp, i32, i32, vp, i64, vp, vp]),
     }

@@ -257,6 +257,13 @@ int eh_code_cyclic(const double* d_H, int n, int s, double* d_B, void* stream);
 int eh_code_decode_table(const double* d_B, int n, int s, const int32_t* d_missing,
                          int64_t n_patterns, double* d_A, void* stream);
 
+/* One-hot feature construction (K15): idx[r,c] = offsets[c] + codes[r,c]; pair features as the
+ * mixed-radix id of two label-encoded columns (arrange_real_data.py:41-64, util.py:49-55). */
+int eh_onehot_assemble(const long long* d_codes, const long long* d_offsets, int64_t rows, int cols,
+                       int32_t* d_idx, void* stream);
+int eh_pair_codes(const long long* d_codes, int64_t rows, int cols, const int32_t* d_pairs, int n_pairs,
+                  const long long* d_radix, long long* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

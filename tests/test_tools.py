@@ -1,0 +1,30 @@
+"""Cluster tool: argument plumbing and host-file outputs (no network)."""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+
+
+def test_get_hosts_writes_reference_files(tmp_path):
+    hf = tmp_path / "inv"
+    hf.write_text("10.0.0.1\n10.0.0.2 extra\n# comment\n")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "cluster.py"), "get_hosts", "--hostfile", str(hf)],
+                       cwd=tmp_path, capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    assert (tmp_path / "hosts").read_text().splitlines()[1] == "10.0.0.2 deeplearning-worker2"   # pytorch_ec2.py:656-708
+    assert (tmp_path / "hosts_address").read_text().split() == ["10.0.0.1", "10.0.0.2"]
+    assert (tmp_path / "hosts_alias").read_text().split()[0] == "deeplearning-worker1"
+
+
+def test_cfg_interpolation():
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    assert cluster.cfg["repo_dir"] == "/shared/erasurehead"
+
+
+def test_makefile_targets_pass_13_positionals():
+    p = subprocess.run(["make", "-n", "approx", "partialcyccoded"], cwd=ROOT, capture_output=True, text=True)
+    assert p.returncode == 0
+    for line in [l for l in p.stdout.splitlines() if "main.py" in l]:
+        assert len(line.split("main.py")[1].split()) >= 13

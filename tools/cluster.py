@@ -1,0 +1,196 @@
+#!/usr/bin/env python
+"""Cluster operations tool (role of the reference's ``tools/pytorch_ec2.py`` + shell helpers).
+
+Sub-commands mirror the reference's command map (pytorch_ec2.py:938-951) where they still make
+sense for GPU nodes:
+
+  launch / shutdown / list_running_instances   EC2 instances through boto3 (only if boto3 is installed)
+  get_hosts                                    write ``hosts``, ``hosts_alias``, ``hosts_address`` (:656-708)
+  run_command  <hostfile> -- <cmd>             run a shell command on every host (paramiko SSH fan-out, :259-299)
+  list_idle_instances <hostfile>               hosts with no GPU compute process (:304-336)
+  kill_python <hostfile>                       stop the training processes this tool started (by recorded PID)
+  setup_nfs <hostfile> <export_dir>            export a directory from the first host and mount it on the rest (:880-900)
+  install <hostfile>                           push SSH keys / build the CUDA library on every host (tools/*.sh role)
+  torchrun --hostfile F --gpus-per-node G -- main.py <13 positionals>
+                                               multi-node launch: one ``torch.distributed.run`` per host
+
+Unlike the reference, processes are never killed by pattern (``pkill python``): the launcher
+records the PID it started on every host under ``~/.erasurehead_b200/pids`` and only those are
+signalled.  Credentials come from the SSH agent / ``~/.ssh/config``; nothing is hard-coded.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import shlex
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from typing import List
+
+PID_DIR = "~/.erasurehead_b200/pids"
+
+
+class Cfg(dict):
+    """Dict with ``%(key)s`` self-interpolation, like the reference's ``Cfg`` (pytorch_ec2.py:12-20)."""
+
+    def __getitem__(self, k):
+        v = dict.__getitem__(self, k)
+        return v % self if isinstance(v, str) and "%(" in v else v
+
+
+cfg = Cfg({
+    "name": "erasurehead", "region": "us-west-2", "availability_zone": "us-west-2b",
+    "instance_type": "p6-b200.48xlarge", "image_id": "", "key_name": "", "ssh_username": "ubuntu",
+    "n_workers": 1, "nfs_mount_point": "/shared", "repo_dir": "%(nfs_mount_point)s/%(name)s",
+})
+
+
+def read_hosts(path: str) -> List[str]:
+    with open(path) as f:
+        return [ln.split()[0] for ln in f if ln.strip() and not ln.startswith("#")]
+
+
+def ssh_run(host: str, command: str, user: str = None, timeout: int = 600):
+    import paramiko
+    cli = paramiko.SSHClient()
+    cli.set_missing_host_key_policy(paramiko.AutoAddPolicy())
+    cli.connect(host, username=user or os.environ.get("EH_SSH_USER"), timeout=30)
+    try:
+        _, out, err = cli.exec_command(command, timeout=timeout)
+        rc = out.channel.recv_exit_status()
+        return rc, out.read().decode(), err.read().decode()
+    finally:
+        cli.close()
+
+
+def fan_out(hosts: List[str], command, user=None):
+    with ThreadPoolExecutor(max_workers=min(32, max(1, len(hosts)))) as ex:
+        futs = {h: ex.submit(ssh_run, h, command(h) if callable(command) else command, user) for h in hosts}
+        res = {}
+        for h, f in futs.items():
+            try:
+                res[h] = f.result()
+            except Exception as e:  # noqa: BLE001
+                res[h] = (255, "", str(e))
+    for h, (rc, out, err) in res.items():
+        print(f"[{h}] rc={rc}\n{out}{err}".rstrip())
+    return res
+
+
+def _ec2():
+    try:
+        import boto3
+    except ImportError:
+        sys.exit("boto3 is not installed: EC2 sub-commands are unavailable here (use a static hostfile)")
+    return boto3.client("ec2", region_name=cfg["region"])
+
+
+def cmd_launch(a):
+    ec2 = _ec2()
+    r = ec2.run_instances(ImageId=cfg["image_id"], InstanceType=cfg["instance_type"], KeyName=cfg["key_name"],
+                          MinCount=a.count, MaxCount=a.count,
+                          Placement={"AvailabilityZone": cfg["availability_zone"]},
+                          TagSpecifications=[{"ResourceType": "instance",
+                                              "Tags": [{"Key": "Name", "Value": cfg["name"]}]}])
+    print("launched", [i["InstanceId"] for i in r["Instances"]])
+
+
+def _instances(states=("running",)):
+    ec2 = _ec2()
+    r = ec2.describe_instances(Filters=[{"Name": "tag:Name", "Values": [cfg["name"]]},
+                                        {"Name": "instance-state-name", "Values": list(states)}])
+    return [i for res in r["Reservations"] for i in res["Instances"]]
+
+
+def cmd_shutdown(a):
+    ids = [i["InstanceId"] for i in _instances(("running", "pending"))]
+    if ids:
+        _ec2().terminate_instances(InstanceIds=ids)
+    print("terminated", ids)
+
+
+def cmd_list_running(a):
+    for i in _instances():
+        print(i["InstanceId"], i.get("PublicIpAddress"), i.get("PrivateIpAddress"))
+
+
+def cmd_get_hosts(a):
+    """hosts: 'ip alias' lines for /etc/hosts; hosts_alias: aliases; hosts_address: private ips."""
+    if a.hostfile:
+        ips = read_hosts(a.hostfile)
+    else:
+        ips = [i["PrivateIpAddress"] for i in _instances()]
+    with open("hosts", "w") as h, open("hosts_alias", "w") as al, open("hosts_address", "w") as ad:
+        for k, ip in enumerate(ips):
+            alias = f"deeplearning-worker{k + 1}"
+            h.write(f"{ip} {alias}\n"); al.write(alias + "\n"); ad.write(ip + "\n")
+    print(f"wrote hosts, hosts_alias, hosts_address ({len(ips)} nodes)")
+
+
+def cmd_run_command(a):
+    fan_out(read_hosts(a.hostfile), " ".join(shlex.quote(x) for x in a.rest))
+
+
+def cmd_list_idle(a):
+    res = fan_out(read_hosts(a.hostfile),
+                  "nvidia-smi --query-compute-apps=pid --format=csv,noheader | wc -l")
+    print("idle:", [h for h, (rc, out, _) in res.items() if rc == 0 and out.strip() == "0"])
+
+
+def cmd_kill_python(a):
+    fan_out(read_hosts(a.hostfile),
+            f"for f in {PID_DIR}/*.pid; do [ -f \"$f\" ] && kill -- -$(cat \"$f\") 2>/dev/null; rm -f \"$f\"; done; true")
+
+
+def cmd_setup_nfs(a):
+    hosts = read_hosts(a.hostfile)
+    head, rest = hosts[0], hosts[1:]
+    d = a.export_dir
+    fan_out([head], f"sudo mkdir -p {d} && echo '{d} *(rw,sync,no_subtree_check,no_root_squash)' | "
+                    "sudo tee -a /etc/exports && sudo exportfs -ra")
+    fan_out(rest, f"sudo mkdir -p {d} && sudo mount -t nfs {head}:{d} {d}")
+
+
+def cmd_install(a):
+    repo = a.repo or cfg["repo_dir"]
+    fan_out(read_hosts(a.hostfile), f"cd {repo} && bash csrc/build.sh | tail -1")
+
+
+def cmd_torchrun(a):
+    hosts = read_hosts(a.hostfile)
+    master = hosts[0]
+    repo = a.repo or os.getcwd()
+    args = " ".join(shlex.quote(x) for x in a.rest)
+
+    def command(h):
+        rank = hosts.index(h)
+        return (f"mkdir -p {PID_DIR} && cd {repo} && setsid python -m torch.distributed.run --nnodes={len(hosts)} "
+                f"--node-rank={rank} --nproc-per-node={a.gpus_per_node} --master-addr {master} "
+                f"--master-port {a.port} {args} > run_node{rank}.log 2>&1 & echo $! > {PID_DIR}/run.pid; wait; "
+                f"tail -5 run_node{rank}.log")
+    fan_out(hosts, command)
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    p = sub.add_parser("launch"); p.add_argument("--count", type=int, default=cfg["n_workers"]); p.set_defaults(fn=cmd_launch)
+    sub.add_parser("shutdown").set_defaults(fn=cmd_shutdown)
+    sub.add_parser("list_running_instances").set_defaults(fn=cmd_list_running)
+    p = sub.add_parser("get_hosts"); p.add_argument("--hostfile"); p.set_defaults(fn=cmd_get_hosts)
+    for name, fn in (("run_command", cmd_run_command), ("list_idle_instances", cmd_list_idle),
+                     ("kill_python", cmd_kill_python), ("kill_all_python", cmd_kill_python), ("install", cmd_install)):
+        p = sub.add_parser(name); p.add_argument("hostfile"); p.add_argument("--repo")
+        p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=fn)
+    p = sub.add_parser("setup_nfs"); p.add_argument("hostfile"); p.add_argument("export_dir"); p.set_defaults(fn=cmd_setup_nfs)
+    p = sub.add_parser("torchrun"); p.add_argument("--hostfile", required=True)
+    p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
+    p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_torchrun)
+    a = ap.parse_args(argv)
+    if getattr(a, "rest", None) and a.rest and a.rest[0] == "--":
+        a.rest = a.rest[1:]
+    a.fn(a)
+
+
+if __name__ == "__main__":
+    main()
