@@ -1,0 +1,228 @@
+// Row-warp variant of the fused dense gradient kernel for narrow matrices (row stride <= 1024
+// floats).  Same contract, scratch, barrier and ship tail as grad_dense.cu; only the consumer
+// mapping differs: LPR lanes own one row (32/LPR rows per warp at a time), so the row dot is a
+// shuffle reduction inside the warp and no block-wide barrier is needed per tile.  Each lane keeps
+// its 4*DVW columns of the row in registers between the forward dot and the rank-1 accumulate;
+// the warps' private accumulators are combined once at the end.
+//
+//   ld <=   32 : LPR =  8, DVW = 1      ld <=  256 : LPR = 32, DVW = 2
+//   ld <=   64 : LPR = 16, DVW = 1      ld <=  512 : LPR = 32, DVW = 4
+//   ld <=  128 : LPR = 32, DVW = 1      ld <= 1024 : LPR = 32, DVW = 8
+#include "grad_dense.cuh"
+
+namespace eh {
+
+template <int LPR, int DVW>
+__global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const GradParams p, const int RB) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int RPW = 32 / LPR;                       // rows a warp processes concurrently
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int G = gridDim.x, b = blockIdx.x;
+    const uint32_t stage_bytes = (uint32_t)RB * p.ld * 4u;
+    float* stages = reinterpret_cast<float*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)p.n_stages * stage_bytes);
+    uint64_t* empty = full + GD_MAX_STAGES;
+    __shared__ uint32_t s_decision;
+
+    const long long my_steps = (b < p.n_steps) ? (p.n_steps - b + G - 1) / G : 0;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.n_stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], GD_CONSUMER_WARPS);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    uint32_t code = DEC_GO;
+    if (warp == GD_CONSUMER_WARPS) {
+        // ---------------- producer warp (identical protocol to grad_dense_kernel)
+        long long issued = 0;
+        uint64_t pol = l2_policy_evict_first();
+        auto issue = [&](long long k) {
+            const long long step = b + k * G;
+            const int sg = (int)(step / p.steps_per_seg);
+            const int row0 = (int)(step % p.steps_per_seg) * RB;
+            const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
+            const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
+            const int st = (int)(k % p.n_stages);
+            mbar_arrive_expect_tx(&full[st], bytes);
+            tma_load_1d(stages + (size_t)st * RB * p.ld, p.seg_X[sg] + (size_t)row0 * p.ld, bytes, &full[st], pol);
+        };
+        if (lane == 0) {
+            const long long pre = my_steps < p.n_stages ? my_steps : p.n_stages;
+            for (; issued < pre; ++issued) issue(issued);
+            code = wait_for_parameters(p);
+            s_decision = code;
+        }
+        __syncwarp();
+        code = __shfl_sync(0xffffffffu, code, 0);
+        asm volatile("bar.sync 1, %0;" ::"r"(GD_THREADS) : "memory");
+        if (code == DEC_SKIP) {
+            if (lane == 0)
+                for (long long k = 0; k < issued; ++k) mbar_wait(&full[(int)(k % p.n_stages)], 0);
+            return;
+        }
+        if (lane == 0) {
+            for (long long k = issued; k < my_steps; ++k) {
+                const int st = (int)(k % p.n_stages);
+                const uint32_t use = (uint32_t)(k / p.n_stages);
+                mbar_wait(&empty[st], (use - 1) & 1);
+                issue(k);
+            }
+        }
+        __syncwarp();
+    } else {
+        asm volatile("bar.sync 1, %0;" ::"r"(GD_THREADS) : "memory");
+        code = s_decision;
+        if (code == DEC_SKIP) return;
+
+        // ---------------- consumers: LPR lanes per row
+        const int ld4 = p.ld >> 2;
+        const int sub = lane / LPR;                     // which of the warp's concurrent rows
+        const int pos = lane % LPR;                     // lane position inside the row
+        float4 bt[DVW], acc[DVW];
+#pragma unroll
+        for (int v = 0; v < DVW; ++v) {
+            const int c = (v * LPR + pos) * 4;
+            acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c + 0 < p.d) t.x = p.beta[c + 0];
+            if (c + 1 < p.d) t.y = p.beta[c + 1];
+            if (c + 2 < p.d) t.z = p.beta[c + 2];
+            if (c + 3 < p.d) t.w = p.beta[c + 3];
+            bt[v] = t;
+        }
+        const int rows_per_pass = GD_CONSUMER_WARPS * RPW;       // rows the CTA covers per pass
+        for (long long k = 0; k < my_steps; ++k) {
+            const int st = (int)(k % p.n_stages);
+            const uint32_t use = (uint32_t)(k / p.n_stages);
+            const long long step = b + k * G;
+            const int sg = (int)(step / p.steps_per_seg);
+            const int row0 = (int)(step % p.steps_per_seg) * RB;
+            const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
+            const float cf = p.coeff[sg];
+            const float* ys = p.seg_y[sg] + row0;
+            mbar_wait(&full[st], use & 1);
+            const float4* tile = reinterpret_cast<const float4*>(stages + (size_t)st * RB * p.ld);
+            for (int r0 = 0; r0 < nr; r0 += rows_per_pass) {
+                const int r = r0 + warp * RPW + sub;
+                const bool valid = r < nr;
+                float4 x[DVW];
+                float dot = 0.f;
+                const float yv = valid ? __ldg(ys + r) : 0.f;
+#pragma unroll
+                for (int v = 0; v < DVW; ++v) {
+                    const int c4 = v * LPR + pos;
+                    x[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (valid && c4 < ld4) x[v] = tile[(size_t)r * ld4 + c4];
+                    dot = fmaf(x[v].x, bt[v].x, dot);
+                    dot = fmaf(x[v].y, bt[v].y, dot);
+                    dot = fmaf(x[v].z, bt[v].z, dot);
+                    dot = fmaf(x[v].w, bt[v].w, dot);
+                }
+#pragma unroll
+                for (int o = LPR / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+                const float rs = valid ? cf * residual(p.model, dot, yv) : 0.f;
+#pragma unroll
+                for (int v = 0; v < DVW; ++v) {
+                    acc[v].x = fmaf(rs, x[v].x, acc[v].x);
+                    acc[v].y = fmaf(rs, x[v].y, acc[v].y);
+                    acc[v].z = fmaf(rs, x[v].z, acc[v].z);
+                    acc[v].w = fmaf(rs, x[v].w, acc[v].w);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[st]);       // the shuffles consumed every lane's tile reads
+        }
+        // ---------------- combine: row groups inside the warp, then the 8 warps through smem
+#pragma unroll
+        for (int o = LPR; o < 32; o <<= 1) {
+#pragma unroll
+            for (int v = 0; v < DVW; ++v) {
+                acc[v].x += __shfl_xor_sync(0xffffffffu, acc[v].x, o);
+                acc[v].y += __shfl_xor_sync(0xffffffffu, acc[v].y, o);
+                acc[v].z += __shfl_xor_sync(0xffffffffu, acc[v].z, o);
+                acc[v].w += __shfl_xor_sync(0xffffffffu, acc[v].w, o);
+            }
+        }
+        asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");      // all tiles consumed: ring is free
+        float4* sacc = reinterpret_cast<float4*>(smem_raw);                    // [8][ld4]
+        if (sub == 0) {
+#pragma unroll
+            for (int v = 0; v < DVW; ++v) {
+                const int c4 = v * LPR + pos;
+                if (c4 < ld4) sacc[warp * ld4 + c4] = acc[v];
+            }
+        }
+        asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
+        float4* mine = reinterpret_cast<float4*>(p.partials + (size_t)b * p.ldp);
+        for (int c4 = tid; c4 < ld4; c4 += GD_CONSUMERS) {
+            float4 t = sacc[c4];
+#pragma unroll
+            for (int w = 1; w < GD_CONSUMER_WARPS; ++w) {
+                const float4 u = sacc[w * ld4 + c4];
+                t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+            }
+            __stcg(mine + c4, t);
+        }
+        asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");      // sacc reads done before the tail reuses smem
+    }
+    reduce_and_ship(p, smem_raw);
+}
+
+template <int LPR, int DVW>
+static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
+    const DevInfo& di = dev_info();
+    constexpr int RPW = 32 / LPR;
+    const int row_bytes = p.ld * 4;
+    // rows per stage: ~32 KB, a multiple of the rows the CTA covers per pass
+    int RB = (32 * 1024) / row_bytes;
+    const int pass = GD_CONSUMER_WARPS * RPW;
+    if (RB < pass) RB = pass;
+    RB = RB / pass * pass;
+    if (RB > p.rows_per_seg) RB = (p.rows_per_seg + pass - 1) / pass * pass;
+    const size_t stage_bytes = (size_t)RB * row_bytes;
+    int stages = (int)((GD_SMEM_BUDGET - 1024) / stage_bytes);
+    if (stages > GD_MAX_STAGES) stages = GD_MAX_STAGES;
+    EH_REQUIRE(stages >= 2, "grad_dense: row tile too large for shared memory (ld=%d)", p.ld);
+    const size_t tail = 2 * GD_MAX_STAGES * sizeof(uint64_t);
+    size_t smem = stages * stage_bytes + tail;
+    const size_t need_red = (size_t)GD_CONSUMER_WARPS * row_bytes;     // sacc + the tail's [8][32] float4
+    if (smem < need_red + tail) smem = need_red + tail;
+    if (smem < 8 * 32 * sizeof(float4) + tail) smem = 8 * 32 * sizeof(float4) + tail;
+    p.n_stages = stages;
+    p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
+    p.n_steps = (long long)p.steps_per_seg * p.n_segs;
+    auto kern = grad_dense_rowwarp_kernel<LPR, DVW>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
+        attr_done = true;
+    }
+    long long grid = di.sm_count;
+    if (grid > p.n_steps) grid = p.n_steps;
+    if (grid < 1) grid = 1;
+    p.ldp = p.ld;
+    const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.ldp * sizeof(float);
+    EH_REQUIRE(scratch_bytes >= need, "grad_dense: scratch too small (%zu < %zu)", scratch_bytes, need);
+    p.hdr = reinterpret_cast<GradScratchHdr*>(d_scratch);
+    p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(d_scratch) + sizeof(GradScratchHdr));
+    int rb = RB;
+    void* args[] = {(void*)&p, (void*)&rb};
+    EH_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream));
+    return EH_OK;
+}
+
+int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
+    if (p.ld <= 32) return launch_rw<8, 1>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 64) return launch_rw<16, 1>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 128) return launch_rw<32, 1>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 256) return launch_rw<32, 2>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 512) return launch_rw<32, 4>(p, d_scratch, scratch_bytes, stream);
+    return launch_rw<32, 8>(p, d_scratch, scratch_bytes, stream);
+}
+
+}  // namespace eh
