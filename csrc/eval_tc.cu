@@ -20,17 +20,11 @@
 // TF32 keeps 10 mantissa bits of X and beta; margins agree with fp32 to ~1e-3 relative, which is
 // below the "%5.3f" resolution of the reference's result files.  `eh_margins_dense` (fp32 CUDA
 // cores) remains available as the exact path.
-#include <cuda.h>
-
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace eh {
 
-constexpr int TC_THREADS = 256;
-constexpr int TC_BM = 128;
-constexpr int TC_BK = 32;                 // floats per stage row = 128 bytes = one swizzle atom
 constexpr int TC_STAGES = 6;
-constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;
 
 struct TcParams {
     long long rows;
@@ -43,71 +37,6 @@ struct TcParams {
     int ldp;
     int col0;           // first iterate handled by this launch
 };
-
-// ---------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
-                                            uint64_t policy) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
-        "[%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
-        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t* smem_result, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)),
-                 "r"(ncols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// 32 lanes x 16 consecutive 32-bit columns: thread i of the warp gets row (lane base + i)
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr)
-        : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// K-major, 128B-swizzled operand tile (rows of 128 bytes, 8-row groups 1024 bytes apart)
-__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
-    uint64_t desc = 0;
-    desc |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);          // start address, bits [0,14)
-    desc |= (uint64_t)1 << 16;                                 // leading byte offset (unused for SW128 K-major)
-    desc |= (uint64_t)(1024 >> 4) << 32;                       // stride byte offset = 8 rows * 128 B
-    desc |= (uint64_t)1 << 46;                                 // descriptor version (Blackwell)
-    desc |= (uint64_t)2 << 61;                                 // SWIZZLE_128B
-    return desc;
-}
-__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
-    return (1u << 4)                 // accumulator F32
-           | (2u << 7)               // A = TF32
-           | (2u << 10)              // B = TF32
-           | (0u << 15) | (0u << 16) // A, B K-major
-           | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
 
 template <int NB>   // BN = 16 * NB accumulator columns
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -196,7 +125,7 @@ eval_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
             const uint32_t as = ti & 1, ause = ti >> 1;
             const long long row = t * TC_BM + q * 32 + lane;
             const bool valid = row < p.rows;
-            const float yv = valid ? __ldg(p.y + row) : 0.f;
+            const float yv = (valid && p.y) ? __ldg(p.y + row) : 0.f;
             mbar_wait(&tfull[as], ause & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
@@ -255,37 +184,6 @@ eval_tc_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
 }
 
 // ---------------------------------------------------------------- host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* ptr = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = (EncodeTiledFn)ptr;
-    }
-    return fn;
-}
-
-static int make_map(CUtensorMap* map, const float* base, uint64_t inner, uint64_t outer, uint64_t ld_elems,
-                    uint32_t box_outer) {
-    EncodeTiledFn fn = encode_fn();
-    EH_REQUIRE(fn, "eval_tc: cuTensorMapEncodeTiled is not available from this driver");
-    cuuint64_t dims[2] = {inner, outer};
-    cuuint64_t strides[1] = {ld_elems * sizeof(float)};
-    cuuint32_t box[2] = {TC_BK, box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    EH_REQUIRE(r == CUDA_SUCCESS, "eval_tc: cuTensorMapEncodeTiled failed (%d)", (int)r);
-    return EH_OK;
-}
-
 template <int NB>
 static int launch_tc(const CUtensorMap& mx, const CUtensorMap& mb, const TcParams& p, cudaStream_t st) {
     constexpr int BN = 16 * NB;

@@ -64,6 +64,16 @@ class WorkerJob(C.Structure):
                 ("coeff", C.c_float * EH_MAX_SEGS)]
 
 
+class McJob(C.Structure):
+    _fields_ = [("d_X", C.c_void_p * EH_MAX_SEGS), ("d_y", C.c_void_p * EH_MAX_SEGS),
+                ("coeff", C.c_float * EH_MAX_SEGS),
+                ("d_W", C.c_void_p), ("d_out", C.c_void_p), ("d_loss", C.c_void_p), ("d_flag", C.c_void_p),
+                ("d_beta_flag", C.c_void_p), ("d_err", C.c_void_p),
+                ("n_segs", C.c_int32), ("rows_per_seg", C.c_int32), ("d", C.c_int32), ("ld", C.c_int32),
+                ("ldw", C.c_int32), ("C", C.c_int32), ("model", C.c_int32), ("stamp", C.c_uint32),
+                ("timeout_ns", C.c_uint64)]
+
+
 class DecoderDesc(C.Structure):
     _fields_ = [("n_workers", C.c_int32), ("n_msgs", C.c_int32), ("n_groups", C.c_int32), ("s", C.c_int32),
                 ("need_private", C.c_int32), ("need_count", C.c_int32), ("need_groups", C.c_int32),
@@ -120,6 +130,8 @@ def _declare(lib):
         "eh_grad_dense": (i32, [P(GradJob), vp, sz, vp]),
         "eh_grad_dense_noalloc_max_ld": (sz, []),
         "eh_grad_dense_noalloc": (i32, [P(GradJob), vp]),
+        "eh_grad_mc_scratch_bytes": (sz, [i64, i32, i32]),
+        "eh_grad_mc": (i32, [P(McJob), vp, sz, vp]),
         "eh_grad_ell_scratch_bytes": (sz, [i32]),
         "eh_grad_ell": (i32, [P(GradEllJob), vp, sz, vp]),
         "eh_decoder_scratch_bytes": (sz, []),

@@ -138,6 +138,33 @@ typedef struct eh_grad_ell_job {
 size_t eh_grad_ell_scratch_bytes(int d);
 int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
 
+/* Multi-column models on the tensor cores (tcgen05.mma kind::tf32 for both products): softmax
+ * regression with C classes (model 2, labels 0..C-1) and C independent logistic columns on the
+ * same data (model 3, labels +-1).  Parameters / gradients use the class-major layout
+ * W[CN][ldw] (CN = 16 for C <= 16, else 32; ldw = d padded to 32) so a C-column model is one flat
+ * vector of CN*ldw floats for the decoder.  d_out (may be peer memory) receives the encoded
+ * gradient, d_loss (optional, zeroed by the caller) the summed loss.  No counterpart in the
+ * reference (single-vector models only); BASELINE.json config "Covertype-shaped multi-class". */
+typedef struct eh_mc_job {
+    const float*    d_X[EH_MAX_SEGS];
+    const float*    d_y[EH_MAX_SEGS];
+    float           coeff[EH_MAX_SEGS];
+    const float*    d_W;            /* [CN, ldw] parameters of this round */
+    float*          d_out;          /* [CN, ldw] destination or NULL (loss only) */
+    double*         d_loss;         /* [1] or NULL */
+    uint32_t*       d_flag;
+    const uint32_t* d_beta_flag;
+    uint32_t*       d_err;
+    int32_t         n_segs, rows_per_seg;
+    int32_t         d, ld, ldw, C;
+    int32_t         model;
+    uint32_t        stamp;
+    uint64_t        timeout_ns;
+} eh_mc_job;
+
+size_t eh_grad_mc_scratch_bytes(int64_t rows_per_seg, int d, int C);
+int eh_grad_mc(const eh_mc_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Decoder round (rank 0): poll arrival flags, apply the injected per-message delay, evaluate
  * the scheme stop rule after every arrival, derive decode weights (sum / first-per-group /

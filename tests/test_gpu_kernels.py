@@ -161,3 +161,42 @@ def test_eval_tc_tensor_core_margins_and_loss(rows, d, R, kind):
     # loss-only call (no margins written) gives the same sums
     sums2, P2 = mops.eval_tc(X, Bt, y, kind=kind, d=d)
     assert P2 is None and torch.allclose(sums, sums2, rtol=1e-12)
+
+
+@pytest.mark.parametrize("rows,d,C,model", [(256, 128, 4, 2), (1000, 200, 7, 2), (4000, 1024, 16, 2),
+                                            (777, 96, 20, 2), (1500, 300, 5, 3), (640, 4096, 16, 2)])
+def test_grad_mc_tensor_core_softmax_and_batched_logistic(rows, d, C, model):
+    """Both tcgen05 products (forward K-major, backward MN-major X^T) vs an fp64 torch reference."""
+    from erasurehead_b200.ops import mc, synth
+    torch.manual_seed(rows + d + C)
+    ld = synth.pad_cols(d)
+    Xs, ys = [], []
+    for _ in range(2):
+        X = torch.zeros(rows, ld, device=DEV)
+        X[:, :d] = torch.randn(rows, d, device=DEV) / np.sqrt(d)
+        Xs.append(X)
+        ys.append(torch.randint(0, C, (rows,), device=DEV).float() if model == 2
+                  else torch.where(torch.rand(rows, device=DEV) > 0.5, 1.0, -1.0))
+    W = torch.randn(d, C, device=DEV)
+    Wp = mc.pack_params(W)
+    cf = [1.0, -0.6]
+    G, loss = mc.grad_mc(Xs, ys, Wp, d, C, coeff=cf, model=model, want_loss=True)
+    want = torch.zeros(d, C, dtype=torch.float64, device=DEV)
+    want_loss = 0.0
+    for X, y, c in zip(Xs, ys, cf):
+        P = X[:, :d].double() @ W.double()
+        if model == 2:
+            S = torch.softmax(P, dim=1)
+            want_loss += -torch.log(S[torch.arange(rows), y.long()]).sum().item()
+            S[torch.arange(rows), y.long()] -= 1.0
+            R = S
+        else:
+            yy = y.double()[:, None]
+            want_loss += torch.nn.functional.softplus(-yy * P).sum().item()
+            R = -yy / (torch.exp(P * yy) + 1)
+        want += X[:, :d].double().t() @ (c * R)
+    got = mc.unpack_params(G, d, C).double()
+    scale = max(1.0, want.abs().max().item())
+    assert (got - want).abs().max().item() <= 4e-3 * scale
+    assert loss.item() == pytest.approx(want_loss, rel=2e-3)
+    assert torch.all(G[C:] == 0)                       # padded classes carry no gradient
