@@ -27,7 +27,20 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
             uint32_t* flag = ws_flag(plan->d_ws_root, lay, wj.worker, wj.msg);
             const float* beta = ws_beta(plan->d_ws_local, lay, par);
             int rc;
-            if (!wj.sparse) {
+            if (wj.sparse == 2) {
+                eh_mc_job j;
+                memset(&j, 0, sizeof(j));
+                for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
+                    j.d_X[i] = (const float*)wj.d_X[i];
+                    j.d_y[i] = wj.d_y[i];
+                    j.coeff[i] = wj.coeff[i];
+                }
+                j.d_W = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
+                j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.ld = wj.ld_or_nnz;
+                j.ldw = (wj.d + 31) / 32 * 32; j.C = wj.classes; j.model = wj.model; j.stamp = stamp;
+                j.timeout_ns = plan->timeout_ns;
+                rc = eh_grad_mc(&j, plan->d_scratch, plan->scratch_bytes, stream);
+            } else if (!wj.sparse) {
                 eh_grad_job j;
                 memset(&j, 0, sizeof(j));
                 for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {

@@ -37,6 +37,29 @@ def _pad32(d: int) -> int:
     return (d + 31) // 32 * 32
 
 
+def _mc_cn(C_: int) -> int:
+    if not 1 <= C_ <= 32:
+        raise ValueError("multi-column models support 1..32 columns on the GPU")
+    return 16 if C_ <= 16 else 32
+
+
+def _mc_flat(d: int, C_: int) -> int:
+    return _mc_cn(C_) * _pad32(d)
+
+
+def pack_mc(W: np.ndarray) -> np.ndarray:
+    """``[..., d, C]`` -> flat class-major padded ``[..., CN * ldw]`` (layout of csrc/grad_mc_tc.cu)."""
+    d, C_ = W.shape[-2:]
+    out = np.zeros(W.shape[:-2] + (_mc_cn(C_), _pad32(d)), dtype=W.dtype)
+    out[..., :C_, :d] = np.swapaxes(W, -1, -2)
+    return out.reshape(W.shape[:-2] + (-1,))
+
+
+def unpack_mc(flat: np.ndarray, d: int, C_: int) -> np.ndarray:
+    W = flat.reshape(flat.shape[:-1] + (_mc_cn(C_), _pad32(d)))[..., :C_, :d]
+    return np.ascontiguousarray(np.swapaxes(W, -1, -2))
+
+
 class Engine:
     """Owns the device state of one run on one rank."""
 
@@ -66,10 +89,10 @@ class Engine:
             first_round=self.first_round)
         self.result: Optional[oracle.RunResult] = None
         self.launches = 0
+        # multi-column models (softmax): parameters travel as one flat class-major vector
+        self.mc = self.model.n_out > 1
+        self.d_eff = _mc_flat(cfg.n_cols, self.model.n_out) if self.mc else cfg.n_cols
         if self.on_gpu:
-            if self.model.n_out != 1:
-                raise NotImplementedError(
-                    "multi-column (softmax) models run through ops.softmax / the CPU engine in this round")
             self._setup_gpu()
 
     # ------------------------------------------------------------------ device set-up
@@ -83,7 +106,7 @@ class Engine:
         self.torch = torch
         L = _lib.lib()
         d = cfg.n_cols
-        self.ws = Workspace(ctx, spec.n, spec.n_msgs, d)
+        self.ws = Workspace(ctx, spec.n, spec.n_msgs, self.d_eff)
         lay = self.ws.lay
         # ---- partitions resident on this GPU (deduplicated across local workers)
         self.parts: Dict[int, tuple] = {}
@@ -105,7 +128,8 @@ class Engine:
                             f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
                             "use fewer partitions per worker")
                 j = _lib.WorkerJob()
-                j.worker, j.msg, j.sparse, j.model = w, kind, int(self.sparse), self.model.device_id
+                j.worker, j.msg, j.sparse, j.model = w, kind, (2 if self.mc else int(self.sparse)), self.model.device_id
+                j.classes = self.model.n_out
                 j.n_segs, j.rows_per_seg, j.d = len(segs), spec.rows_per_part, d
                 X0 = self.parts[segs[0].partition][0]
                 j.ld_or_nnz = X0.shape[1] if self.sparse else X0.stride(0)
@@ -118,6 +142,10 @@ class Engine:
         self.n_jobs = len(jobs)
         ld_max = max([_pad32(d)] + [self.parts[p][0].stride(0) for p in needed if not self.sparse])
         sb = max(L.eh_grad_dense_scratch_bytes(int(ld_max)), L.eh_grad_ell_scratch_bytes(int(d)))
+        if self.mc:
+            if self.sparse:
+                raise NotImplementedError("multi-column models need dense features")
+            sb = max(sb, L.eh_grad_mc_scratch_bytes(int(spec.rows_per_part), int(d), int(self.model.n_out)))
         self.scratch = gops.Scratch(sb, dev)
         self.timeout_ns = int(120e9)
         # ---- decoder state (root)
@@ -144,6 +172,8 @@ class Engine:
                 raise ValueError("no dataset given and cfg.synthetic is off")
             from .ops import synth
             task = 1 if self.model.name == "linear" else 0
+            if self.mc:
+                raise ValueError("on-device synthetic data is binary; pass a dataset for multi-class models")
             return synth.synth_gmm(spec.rows_per_part, cfg.n_cols, cfg.seed or 0, p, task, dev)
         y = torch.as_tensor(np.ascontiguousarray(self.data.labels(p)), dtype=torch.float32).to(dev)
         if self.sparse:
@@ -159,7 +189,7 @@ class Engine:
         torch = self.torch
         from .ops import _lib, codegen
         cfg, spec, dev = self.cfg, self.spec, self.ctx.device
-        n, d, R = spec.n, cfg.n_cols, cfg.rounds
+        n, d, R = spec.n, self.d_eff, cfg.rounds
         t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(dev)
         self.t_group = t(spec.group_of, torch.int32)
         self.t_B = t(spec.B, torch.float64) if spec.B is not None else None
@@ -175,8 +205,8 @@ class Engine:
         dl[~np.isfinite(self.delays)] = np.uint64(NEVER_NS)
         self.t_delay = torch.from_numpy(dl.view(np.int64)).to(dev)
         self.t_eta = t(cfg.learning_rates(), torch.float64)
-        self.t_beta64 = t(self.beta0, torch.float64)
-        self.t_u64 = t(self.u0, torch.float64)
+        self.t_beta64 = t(pack_mc(self.beta0) if self.mc else self.beta0, torch.float64)
+        self.t_u64 = t(pack_mc(self.u0) if self.mc else self.u0, torch.float64)
         self.t_betaset = torch.zeros((R, d), dtype=torch.float64, device=dev)
         self.t_timeset = torch.zeros(R, dtype=torch.float64, device=dev)
         self.t_wts = torch.full((R, n), -1.0, dtype=torch.float64, device=dev)
@@ -250,7 +280,7 @@ class Engine:
         r = self._cursor - self.first_round
         if self.dec is not None:
             if not hasattr(self, "_pin_in"):
-                n, d = self.spec.n, self.cfg.n_cols
+                n, d = self.spec.n, self.d_eff
                 self._pin_in = torch.empty(n + 1, dtype=torch.int64).pin_memory()
                 self._pin_out = torch.empty(d + 1, dtype=torch.float64).pin_memory()
                 self.h2d_bytes = (n + 1) * 8
@@ -266,7 +296,7 @@ class Engine:
             self.t_eta[r:r + 1].view(torch.int64).copy_(self._pin_in[n:], non_blocking=True)
         self.enqueue(1)
         if self.dec is not None:
-            d = self.cfg.n_cols
+            d = self.d_eff
             self._pin_out[:d].copy_(self.t_betaset[r], non_blocking=True)
             self._pin_out[d:].copy_(self.t_timeset[r:r + 1], non_blocking=True)
             torch.cuda.current_stream().synchronize()
@@ -314,10 +344,13 @@ class Engine:
 
     def _collect(self, R: int) -> oracle.RunResult:
         cpu = lambda t: t[:R].detach().cpu().numpy()
+        betaset, u, beta = cpu(self.t_betaset), self.t_u64.cpu().numpy(), self.t_beta64.cpu().numpy()
+        if self.mc:
+            dd, cc = self.cfg.n_cols, self.model.n_out
+            betaset, u, beta = unpack_mc(betaset, dd, cc), unpack_mc(u, dd, cc), unpack_mc(beta, dd, cc)
         return oracle.RunResult(
-            betaset=cpu(self.t_betaset), timeset=cpu(self.t_timeset), worker_timeset=cpu(self.t_wts),
-            weights=cpu(self.t_weights), n_collected=cpu(self.t_ncol).astype(np.int64),
-            u=self.t_u64.cpu().numpy(), beta=self.t_beta64.cpu().numpy())
+            betaset=betaset, timeset=cpu(self.t_timeset), worker_timeset=cpu(self.t_wts),
+            weights=cpu(self.t_weights), n_collected=cpu(self.t_ncol).astype(np.int64), u=u, beta=beta)
 
     # ------------------------------------------------------------------ evaluation
     def evaluate(self, res: Optional[oracle.RunResult] = None):
@@ -330,9 +363,32 @@ class Engine:
             return results.evaluate_host(self.model, self.data, res.betaset, self.cfg.compat)
         return self._evaluate_gpu(res.betaset)
 
+    def _evaluate_gpu_mc(self, betaset: np.ndarray):
+        """Cross-entropy of every iterate: the forward tensor-core product + loss epilogue."""
+        from . import results
+        from .ops import mc
+        torch = self.torch
+        dev, cfg, spec = self.ctx.device, self.cfg, self.spec
+        R, d, C_ = betaset.shape
+        n_parts = spec.n_partitions - (1 if cfg.compat and spec.n_partitions > 1 else 0)
+        Xt, yt = self._device_test()
+        tr, te = np.zeros(R), np.zeros(R)
+        for i in range(R):
+            Wp = torch.from_numpy(pack_mc(betaset[i]).astype(np.float32)).to(dev)
+            tot, rows = 0.0, 0
+            for p in range(n_parts):
+                Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
+                tot += float(mc.loss_mc(Xp, yp, Wp, d, C_, self.model.device_id).item())
+                rows += Xp.shape[0]
+            tr[i] = tot / rows
+            te[i] = float(mc.loss_mc(Xt, yt, Wp, d, C_, self.model.device_id).item()) / Xt.shape[0]
+        return results.Evaluation(tr, te, None)
+
     def _evaluate_gpu(self, betaset: np.ndarray):
         from . import results
         from .ops import metrics as mops
+        if self.mc:
+            return self._evaluate_gpu_mc(betaset)
         torch = self.torch
         dev = self.ctx.device
         cfg, spec = self.cfg, self.spec
@@ -396,6 +452,9 @@ class Engine:
         index so no RNG state is needed (delays.py)."""
         if self.on_gpu:
             beta, u = self.t_beta64.cpu().numpy(), self.t_u64.cpu().numpy()
+            if self.mc:
+                beta, u = (unpack_mc(beta, self.cfg.n_cols, self.model.n_out),
+                           unpack_mc(u, self.cfg.n_cols, self.model.n_out))
         else:
             beta, u = self.result.beta, self.result.u
         np.savez(path, next_round=next_round, beta=beta, u=u,

@@ -59,7 +59,7 @@ class GradEllJob(C.Structure):
 class WorkerJob(C.Structure):
     _fields_ = [("worker", C.c_int32), ("msg", C.c_int32), ("sparse", C.c_int32), ("model", C.c_int32),
                 ("n_segs", C.c_int32), ("rows_per_seg", C.c_int32), ("d", C.c_int32), ("ld_or_nnz", C.c_int32),
-                ("bias_col", C.c_int32), ("reserved", C.c_int32),
+                ("bias_col", C.c_int32), ("classes", C.c_int32),
                 ("d_X", C.c_void_p * EH_MAX_SEGS), ("d_y", C.c_void_p * EH_MAX_SEGS),
                 ("coeff", C.c_float * EH_MAX_SEGS)]
 

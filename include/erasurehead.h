@@ -221,11 +221,11 @@ int eh_decoder_publish(const eh_decoder_desc* desc, int round, void* stream);
 typedef struct eh_worker_job {
     int32_t  worker;                 /* global worker id (slot row on the root) */
     int32_t  msg;                    /* EH_MSG_CODED / EH_MSG_PRIVATE */
-    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL */
+    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL, 2: dense multi-column (tensor cores) */
     int32_t  model;
     int32_t  n_segs, rows_per_seg;
     int32_t  d, ld_or_nnz;           /* dense: row stride; ELL: ones per row */
-    int32_t  bias_col, reserved;
+    int32_t  bias_col, classes;      /* classes: columns of a multi-column model (kind 2) */
     const void*  d_X[EH_MAX_SEGS];   /* float* rows or int32* indices */
     const float* d_y[EH_MAX_SEGS];
     float    coeff[EH_MAX_SEGS];

@@ -143,3 +143,32 @@ def test_nccl_baseline_engine_matches_oracle_single_gpu():
     eng.prepare(); eng.enqueue(4); eng.finish()
     ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl)
     assert np.abs(eng.beta.cpu().numpy() - ref.betaset[-1]).max() <= 5e-4 * max(1.0, np.abs(ref.betaset).max())
+
+
+def test_engine_softmax_multiclass_matches_oracle():
+    """Multi-class softmax regression through the full coded path (tcgen05 gradient kernels)."""
+    C_ = 5
+    cfg = mk("approx", s=1, k=6, rows=8 * 512, d=160, model="softmax", classes=C_, eta0=0.5, rounds=5)
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1, task="softmax", classes=C_)
+    dl = spaced_delays(cfg.rounds, 8, seed=4)
+    eng = Engine(cfg, data, delays=dl)
+    res = eng.run()
+    assert res.betaset.shape == (5, 160, C_)
+    ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl, beta0=eng.beta0, model=eng.model)
+    scale = max(1.0, np.abs(ref.betaset).max())
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-3 * scale        # TF32 operands
+    assert np.array_equal(res.n_collected, ref.n_collected)
+    ev = eng.evaluate(res)
+    from erasurehead_b200 import results
+    evh = results.evaluate_host(eng.model, data, res.betaset)
+    assert np.allclose(ev.training_loss, evh.training_loss, rtol=3e-3)
+    assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=3e-3)
+    assert ev.training_loss[-1] < ev.training_loss[0]
+    eng.close()
+    # exact coded scheme on the same data: decode weights act on the flat multi-column vector
+    cfg2 = mk("coded", s=2, seed=3, rows=8 * 512, d=160, model="softmax", classes=C_, eta0=0.5, rounds=4)
+    eng2 = Engine(cfg2, data, delays=spaced_delays(4, 8, seed=6))
+    r2 = eng2.run()
+    ref2 = oracle.run_rounds(cfg2, build_scheme(cfg2, eng2.spec.B), data, eng2.delays, beta0=eng2.beta0, model=eng2.model)
+    assert np.abs(r2.betaset - ref2.betaset).max() <= 1e-2 * max(1.0, np.abs(ref2.betaset).max())
+    eng2.close()
