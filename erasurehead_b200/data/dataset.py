@@ -43,10 +43,12 @@ class Dataset:
         r = self.rows_per_part
         return self.y[p * r:(p + 1) * r]
 
-    def train_matrix(self, compat_skip_last: bool = False):
-        """All training rows.  ``compat_skip_last`` reproduces Q1 (naive.py:159-172: the
-        evaluation loop ``range(2, n_procs-1)`` never loads the last partition)."""
-        parts = self.parts[:-1] if compat_skip_last and len(self.parts) > 1 else self.parts
+    def train_matrix(self, n_eval_parts: Optional[int] = None):
+        """Training rows used by the evaluation epilogue.  ``n_eval_parts`` limits it to the first
+        partitions: the reference's loop ``for j in range(2, n_procs-1)`` (naive.py:159-172,
+        partial_coded.py:243-254) loads files ``1 .. n_procs-2`` only -- Q1, reproduced in compat
+        mode by passing ``n_workers - 1``."""
+        parts = self.parts if n_eval_parts is None else self.parts[:max(1, n_eval_parts)]
         X = sp_vstack(parts).tocsr() if self.is_sparse else np.vstack(parts)
         return X, self.y[:X.shape[0]]
 

@@ -360,8 +360,12 @@ class Engine:
         if not self.ctx.is_root or res is None:
             return None
         if not self.on_gpu:
-            return results.evaluate_host(self.model, self.data, res.betaset, self.cfg.compat)
+            return results.evaluate_host(self.model, self.data, res.betaset, self._n_eval_parts())
         return self._evaluate_gpu(res.betaset)
+
+    def _n_eval_parts(self):
+        """Q1: the reference evaluates on files 1..n_procs-2 only; None = all partitions."""
+        return max(1, self.spec.n - 1) if self.cfg.compat else None
 
     def _evaluate_gpu_mc(self, betaset: np.ndarray):
         """Cross-entropy of every iterate: the forward tensor-core product + loss epilogue."""
@@ -370,7 +374,7 @@ class Engine:
         torch = self.torch
         dev, cfg, spec = self.ctx.device, self.cfg, self.spec
         R, d, C_ = betaset.shape
-        n_parts = spec.n_partitions - (1 if cfg.compat and spec.n_partitions > 1 else 0)
+        n_parts = self._n_eval_parts() or spec.n_partitions
         Xt, yt = self._device_test()
         tr, te = np.zeros(R), np.zeros(R)
         for i in range(R):
@@ -396,7 +400,7 @@ class Engine:
         Bt = torch.zeros((R, _pad32(d)), dtype=torch.float32, device=dev)
         Bt[:, :d] = torch.from_numpy(betaset).to(dev)
         kind = 1 if self.model.name == "linear" else 0
-        n_parts = spec.n_partitions - (1 if cfg.compat and spec.n_partitions > 1 else 0)   # Q1
+        n_parts = self._n_eval_parts() or spec.n_partitions                                # Q1
         tr = torch.zeros(R, dtype=torch.float64, device=dev)
         rows = 0
         # dense data: one tcgen05/TMEM pass over X evaluates all R iterates with the loss fused in

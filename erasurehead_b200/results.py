@@ -26,9 +26,9 @@ class Evaluation:
     auc: Optional[np.ndarray]
 
 
-def evaluate_host(model, data, betaset: np.ndarray, compat_skip_last: bool = False) -> Evaluation:
+def evaluate_host(model, data, betaset: np.ndarray, n_eval_parts=None) -> Evaluation:
     """Float64 numpy evaluation of all iterates (one matmul for all rounds)."""
-    X_tr, y_tr = data.train_matrix(compat_skip_last)
+    X_tr, y_tr = data.train_matrix(n_eval_parts)
     X_te, y_te = data.X_test, data.y_test
     R = betaset.shape[0]
     tr, te = np.zeros(R), np.zeros(R)
