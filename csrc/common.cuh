@@ -39,6 +39,10 @@ struct DevInfo {
 const DevInfo& dev_info();
 // Process-wide launch sequence number for the decision word of the cooperative gradient kernels.
 uint32_t next_launch_seq();
+// Launch a kernel whose CTAs wait on one another (device-wide barrier).  Cooperative by default so
+// co-residency is guaranteed; EH_LAUNCH=plain uses an ordinary launch (grid <= resident capacity is
+// still enforced by the callers; safe while every kernel of the process runs in one stream).
+int launch_grid_sync(const void* kern, dim3 grid, dim3 block, void** args, size_t smem, cudaStream_t stream);
 
 // ---------------------------------------------------------------- workspace control block
 // Lives at lay.off_ctl in every GPU's workspace.  128-byte separated words.

@@ -347,8 +347,7 @@ extern "C" int eh_decoder_round(const eh_decoder_desc* D, int round, int r, void
     eh_decoder_desc desc = *D;
     int round_ = round, r_ = r;
     void* args[] = {(void*)&desc, (void*)&round_, (void*)&r_};
-    EH_CUDA(cudaLaunchCooperativeKernel((void*)decoder_round_kernel, dim3(grid), dim3(DEC_THREADS), args, 0,
-                                        (cudaStream_t)stream));
+    { int lrc = launch_grid_sync((const void*)decoder_round_kernel, dim3(grid), dim3(DEC_THREADS), args, 0, (cudaStream_t)stream); if (lrc) return lrc; }
     return EH_OK;
 }
 

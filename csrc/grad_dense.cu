@@ -216,7 +216,7 @@ static int launch(const eh_grad_job* j, GradParams& p, void* d_scratch, size_t s
     p.hdr = reinterpret_cast<GradScratchHdr*>(d_scratch);
     p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(d_scratch) + sizeof(GradScratchHdr));
     void* args[] = {(void*)&p};
-    EH_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream));
+    { int lrc = launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream); if (lrc) return lrc; }
     (void)j;
     return EH_OK;
 }
@@ -227,7 +227,9 @@ extern "C" size_t eh_grad_dense_scratch_bytes(int d) {
     const int ld = (d + 3) & ~3;
     int sm = eh::dev_info().sm_count;
     if (sm <= 0) sm = 160;
-    return sizeof(eh::GradScratchHdr) + (size_t)sm * (size_t)(ld + 32) * sizeof(float);
+    size_t b = sizeof(eh::GradScratchHdr) + (size_t)sm * (size_t)(ld + 32) * sizeof(float);
+    const size_t wide = 1024 + ((size_t)65536 + ld) * sizeof(float);      // two-pass fallback (ld > 8192)
+    return b > wide ? b : wide;
 }
 
 extern "C" int eh_grad_dense(const eh_grad_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
@@ -237,7 +239,6 @@ extern "C" int eh_grad_dense(const eh_grad_job* j, void* d_scratch, size_t scrat
                EH_MAX_SEGS);
     EH_REQUIRE(j->rows_per_seg > 0 && j->d > 0, "grad_dense: empty problem");
     EH_REQUIRE(j->ld >= j->d && (j->ld % 4) == 0, "grad_dense: ld (%d) must be >= d and a multiple of 4", j->ld);
-    EH_REQUIRE(j->ld <= 8192, "grad_dense: ld=%d > 8192 not supported by the one-pass kernel", j->ld);
     GradParams p;
     memset(&p, 0, sizeof(p));
     for (int i = 0; i < j->n_segs; ++i) {
@@ -254,6 +255,7 @@ extern "C" int eh_grad_dense(const eh_grad_job* j, void* d_scratch, size_t scrat
     p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     cudaStream_t st = (cudaStream_t)stream;
+    if (j->ld > 8192) return launch_wide(p, d_scratch, scratch_bytes, st);
     if (j->ld <= 1024) return launch_rowwarp(p, d_scratch, scratch_bytes, st);
     if (j->ld <= 2048) return launch<2, 8>(j, p, d_scratch, scratch_bytes, st);
     if (j->ld <= 4096) return launch<4, 4>(j, p, d_scratch, scratch_bytes, st);

@@ -138,5 +138,6 @@ __device__ __forceinline__ uint32_t wait_for_parameters(const GradParams& p) {
 
 // host-side launchers (defined next to their kernels)
 int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
+int launch_wide(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
 
 }  // namespace eh

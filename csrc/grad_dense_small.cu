@@ -212,7 +212,7 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
     p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(d_scratch) + sizeof(GradScratchHdr));
     int rb = RB;
     void* args[] = {(void*)&p, (void*)&rb};
-    EH_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream));
+    { int lrc = launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream); if (lrc) return lrc; }
     return EH_OK;
 }
 

@@ -167,7 +167,6 @@ extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scr
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
     void* args[] = {(void*)&p};
-    EH_CUDA(cudaLaunchCooperativeKernel((void*)grad_ell_kernel, dim3((unsigned)grid), dim3(GE_THREADS), args, 0,
-                                        (cudaStream_t)stream));
+    { int lrc = launch_grid_sync((const void*)grad_ell_kernel, dim3((unsigned)grid), dim3(GE_THREADS), args, 0, (cudaStream_t)stream); if (lrc) return lrc; }
     return EH_OK;
 }

@@ -5,6 +5,7 @@
 // every worker GPU stores into directly over NVLink; the per-round `Isend(beta)` loop
 // (naive.py:97-98) becomes peer stores into each GPU's `beta[2][d]` buffer.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "workspace.cuh"
 
@@ -43,6 +44,21 @@ uint32_t next_launch_seq() {
     const uint32_t v = seq++;
     if (seq >= (1u << 30)) seq = 1;
     return v;
+}
+
+int launch_grid_sync(const void* kern, dim3 grid, dim3 block, void** args, size_t smem, cudaStream_t stream) {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("EH_LAUNCH");
+        mode = (e && strcmp(e, "plain") == 0) ? 1 : 0;
+    }
+    cudaError_t err = mode ? cudaLaunchKernel(kern, grid, block, args, smem, stream)
+                           : cudaLaunchCooperativeKernel(kern, grid, block, args, smem, stream);
+    if (err != cudaSuccess) {
+        set_error("kernel launch failed: %s", cudaGetErrorString(err));
+        return (int)err;
+    }
+    return EH_OK;
 }
 
 static inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }

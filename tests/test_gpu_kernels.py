@@ -20,7 +20,8 @@ def ref_grad(X, y, beta, coeff, model):
     return X.t() @ (coeff * r)
 
 
-@pytest.mark.parametrize("rows,d", [(64, 16), (1000, 100), (517, 1024), (300, 1500), (1024, 4096), (96, 8000)])
+@pytest.mark.parametrize("rows,d", [(64, 16), (1000, 100), (517, 1024), (300, 1500), (1024, 4096), (96, 8000),
+                                    (700, 20000)])
 @pytest.mark.parametrize("model", [0, 1])
 def test_grad_dense_matches_reference(rows, d, model):
     from erasurehead_b200.ops import grad, synth
