@@ -19,6 +19,16 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
         const int round = first_round + it;
         const int par = round & 1;
         const uint32_t stamp = (uint32_t)round + 1u;
+        // dense single-vector messages of one shape are batched into one launch (<= 8 messages,
+        // <= 32 partitions); one-hot and multi-column messages get their own kernels
+        eh_grad_job batch[8];
+        int nb = 0, nb_segs = 0;
+        auto flush = [&]() -> int {
+            if (nb == 0) return EH_OK;
+            int rc = eh_grad_dense_multi(batch, nb, plan->d_scratch, plan->scratch_bytes, stream);
+            nb = 0; nb_segs = 0;
+            return rc;
+        };
         for (int q = 0; q < plan->n_jobs; ++q) {
             const eh_worker_job& wj = plan->jobs[q];
             EH_REQUIRE(wj.worker >= 0 && wj.worker < (int)lay.n_workers && wj.msg >= 0 && wj.msg < (int)lay.n_msgs,
@@ -26,8 +36,10 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
             float* out = ws_slot(plan->d_ws_root, lay, wj.worker, wj.msg, par);
             uint32_t* flag = ws_flag(plan->d_ws_root, lay, wj.worker, wj.msg);
             const float* beta = ws_beta(plan->d_ws_local, lay, par);
-            int rc;
+            int rc = EH_OK;
             if (wj.sparse == 2) {
+                rc = flush();
+                if (rc) return rc;
                 eh_mc_job j;
                 memset(&j, 0, sizeof(j));
                 for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
@@ -51,8 +63,18 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.d_beta = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.ld = wj.ld_or_nnz;
                 j.model = wj.model; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
-                rc = eh_grad_dense(&j, plan->d_scratch, plan->scratch_bytes, stream);
+                const bool fits = nb < 8 && nb_segs + j.n_segs <= 32 &&
+                                  (nb == 0 || (batch[0].d == j.d && batch[0].ld == j.ld &&
+                                               batch[0].rows_per_seg == j.rows_per_seg && batch[0].model == j.model));
+                if (!fits) {
+                    rc = flush();
+                    if (rc) return rc;
+                }
+                batch[nb++] = j;
+                nb_segs += j.n_segs;
             } else {
+                rc = flush();
+                if (rc) return rc;
                 eh_grad_ell_job j;
                 memset(&j, 0, sizeof(j));
                 for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
@@ -65,6 +87,10 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.model = wj.model; j.bias_col = wj.bias_col; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
                 rc = eh_grad_ell(&j, plan->d_scratch, plan->scratch_bytes, stream);
             }
+            if (rc) return rc;
+        }
+        {
+            int rc = flush();
             if (rc) return rc;
         }
         if (plan->decoder) {

@@ -36,7 +36,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
     float* red = reinterpret_cast<float*>(empty + GD_MAX_STAGES);      // [2][8][RB]
     __shared__ uint32_t s_decision;
 
-    const long long my_steps = (b < p.n_steps) ? (p.n_steps - b + G - 1) / G : 0;
+    const JobView jv = job_of_cta(p);
+    const long long my_steps = (jv.bl < jv.n_steps) ? (jv.n_steps - jv.bl + jv.Gj - 1) / jv.Gj : 0;
 
     if (tid == 0) {
         for (int s = 0; s < p.n_stages; ++s) {
@@ -56,8 +57,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
         if (lane == 0) {
             const long long pre = my_steps < p.n_stages ? my_steps : p.n_stages;
             for (; issued < pre; ++issued) {
-                const long long step = b + issued * G;
-                const int sg = (int)(step / p.steps_per_seg);
+                const long long step = jv.bl + issued * (long long)jv.Gj;
+                const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
                 const int row0 = (int)(step % p.steps_per_seg) * RB;
                 const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
                 const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
@@ -85,8 +86,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
                 const int st = (int)(k % p.n_stages);
                 const uint32_t use = (uint32_t)(k / p.n_stages);      // >= 1 here
                 mbar_wait(&empty[st], (use - 1) & 1);
-                const long long step = b + k * G;
-                const int sg = (int)(step / p.steps_per_seg);
+                const long long step = jv.bl + k * (long long)jv.Gj;
+                const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
                 const int row0 = (int)(step % p.steps_per_seg) * RB;
                 const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
                 const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
@@ -118,8 +119,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
         for (long long k = 0; k < my_steps; ++k) {
             const int st = (int)(k % p.n_stages);
             const uint32_t use = (uint32_t)(k / p.n_stages);
-            const long long step = b + k * G;
-            const int sg = (int)(step / p.steps_per_seg);
+            const long long step = jv.bl + k * (long long)jv.Gj;
+            const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
             const int row0 = (int)(step % p.steps_per_seg) * RB;
             const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
             // labels / encode weight of this tile (independent of the TMA data)
@@ -188,8 +189,34 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
 
 // ------------------------------------------------------------------------------------ host
 
+// CTA ranges of the batched messages, proportional to their tile counts; every message gets at
+// least one CTA and never more CTAs than tiles.  Returns the grid size.
+int assign_ctas(GradParams& p, int sm_count) {
+    long long total = 0;
+    long long steps[GD_MAX_JOBS];
+    for (int j = 0; j < p.n_jobs; ++j) {
+        steps[j] = (long long)p.steps_per_seg * p.job_nsegs[j];
+        total += steps[j];
+    }
+    long long grid = sm_count;
+    if (grid > total) grid = total;
+    if (grid < p.n_jobs) grid = p.n_jobs;
+    // one CTA each, the rest in proportion to the tile counts (never more CTAs than tiles)
+    const long long spare = grid - p.n_jobs;
+    int used = 0;
+    p.job_cta0[0] = 0;
+    for (int j = 0; j < p.n_jobs; ++j) {
+        long long g = 1 + (total > 0 ? spare * steps[j] / total : 0);
+        if (g > steps[j]) g = steps[j];
+        if (g < 1) g = 1;
+        used += (int)g;
+        p.job_cta0[j + 1] = used;
+    }
+    return used;
+}
+
 template <int DV, int RB>
-static int launch(const eh_grad_job* j, GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
+static int launch(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
     const DevInfo& di = dev_info();
     const size_t stage_bytes = (size_t)RB * p.ld * 4;
     int stages = (int)((GD_SMEM_BUDGET - 1024) / stage_bytes);
@@ -200,25 +227,79 @@ static int launch(const eh_grad_job* j, GradParams& p, void* d_scratch, size_t s
     if (smem < 8 * 32 * sizeof(float4) + tail) smem = 8 * 32 * sizeof(float4) + tail;
     p.n_stages = stages;
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
-    p.n_steps = (long long)p.steps_per_seg * p.n_segs;
     auto kern = grad_dense_kernel<DV, RB>;
     static bool attr_done = false;
     if (!attr_done) {
         EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
         attr_done = true;
     }
-    long long grid = di.sm_count;
-    if (grid > p.n_steps) grid = p.n_steps;
-    if (grid < 1) grid = 1;
+    const int grid = assign_ctas(p, di.sm_count);
     p.ldp = p.ld;
     const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.ldp * sizeof(float);
     EH_REQUIRE(scratch_bytes >= need, "grad_dense: scratch too small (%zu < %zu)", scratch_bytes, need);
     p.hdr = reinterpret_cast<GradScratchHdr*>(d_scratch);
     p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(d_scratch) + sizeof(GradScratchHdr));
     void* args[] = {(void*)&p};
-    { int lrc = launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream); if (lrc) return lrc; }
-    (void)j;
-    return EH_OK;
+    return launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(GD_THREADS), args, smem, stream);
+}
+
+static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes, void* stream) {
+    EH_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= GD_MAX_JOBS && d_scratch, "grad_dense: bad job list (1..%d messages)",
+               GD_MAX_JOBS);
+    const eh_grad_job* j0 = &jobs[0];
+    EH_REQUIRE(j0->d_beta, "grad_dense: null parameters");
+    EH_REQUIRE(j0->rows_per_seg > 0 && j0->d > 0, "grad_dense: empty problem");
+    EH_REQUIRE(j0->ld >= j0->d && (j0->ld % 4) == 0, "grad_dense: ld (%d) must be >= d and a multiple of 4", j0->ld);
+    GradParams p;
+    memset(&p, 0, sizeof(p));
+    int nseg = 0;
+    for (int q = 0; q < n_jobs; ++q) {
+        const eh_grad_job* j = &jobs[q];
+        EH_REQUIRE(j->d_out, "grad_dense: null destination");
+        EH_REQUIRE(j->n_segs > 0 && j->n_segs <= EH_MAX_SEGS, "grad_dense: n_segs=%d out of range (1..%d)", j->n_segs,
+                   EH_MAX_SEGS);
+        EH_REQUIRE(j->d == j0->d && j->ld == j0->ld && j->rows_per_seg == j0->rows_per_seg && j->model == j0->model &&
+                       j->d_beta == j0->d_beta && j->d_beta_flag == j0->d_beta_flag && j->stamp == j0->stamp,
+                   "grad_dense: batched messages must share shape, model, parameters and stamp");
+        EH_REQUIRE(nseg + j->n_segs <= GD_TOTAL_SEGS, "grad_dense: more than %d partitions in one batch", GD_TOTAL_SEGS);
+        p.job_seg0[q] = nseg;
+        p.job_nsegs[q] = j->n_segs;
+        p.job_out[q] = j->d_out;
+        p.job_flag[q] = j->d_flag;
+        for (int i = 0; i < j->n_segs; ++i, ++nseg) {
+            EH_REQUIRE(j->d_X[i] && j->d_y[i], "grad_dense: null segment %d", i);
+            EH_REQUIRE(((uintptr_t)j->d_X[i] % 16) == 0, "grad_dense: X must be 16-byte aligned");
+            p.seg_X[nseg] = j->d_X[i];
+            p.seg_y[nseg] = j->d_y[i];
+            p.coeff[nseg] = j->coeff[i];
+        }
+    }
+    p.n_jobs = n_jobs;
+    p.beta = j0->d_beta; p.beta_flag = j0->d_beta_flag; p.err = j0->d_err;
+    p.d = j0->d; p.ld = j0->ld;
+    p.rows_per_seg = j0->rows_per_seg; p.model = j0->model;
+    p.stamp = j0->stamp; p.seq = next_launch_seq();
+    p.timeout_ns = j0->timeout_ns ? j0->timeout_ns : 30ull * 1000000000ull;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (p.ld > 8192) {
+        // two-pass fallback handles one message at a time
+        for (int q = 0; q < n_jobs; ++q) {
+            GradParams w = p;
+            for (int i = 0; i < p.job_nsegs[q]; ++i) {
+                w.seg_X[i] = p.seg_X[p.job_seg0[q] + i];
+                w.seg_y[i] = p.seg_y[p.job_seg0[q] + i];
+                w.coeff[i] = p.coeff[p.job_seg0[q] + i];
+            }
+            w.n_segs = p.job_nsegs[q]; w.out = p.job_out[q]; w.flag = p.job_flag[q];
+            int rc = launch_wide(w, d_scratch, scratch_bytes, st);
+            if (rc) return rc;
+        }
+        return EH_OK;
+    }
+    if (p.ld <= 1024) return launch_rowwarp(p, d_scratch, scratch_bytes, st);
+    if (p.ld <= 2048) return launch<2, 8>(p, d_scratch, scratch_bytes, st);
+    if (p.ld <= 4096) return launch<4, 4>(p, d_scratch, scratch_bytes, st);
+    return launch<8, 2>(p, d_scratch, scratch_bytes, st);
 }
 
 }  // namespace eh
@@ -233,33 +314,12 @@ extern "C" size_t eh_grad_dense_scratch_bytes(int d) {
 }
 
 extern "C" int eh_grad_dense(const eh_grad_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
-    using namespace eh;
-    EH_REQUIRE(j && j->d_beta && j->d_out && d_scratch, "grad_dense: null pointer");
-    EH_REQUIRE(j->n_segs > 0 && j->n_segs <= EH_MAX_SEGS, "grad_dense: n_segs=%d out of range (1..%d)", j->n_segs,
-               EH_MAX_SEGS);
-    EH_REQUIRE(j->rows_per_seg > 0 && j->d > 0, "grad_dense: empty problem");
-    EH_REQUIRE(j->ld >= j->d && (j->ld % 4) == 0, "grad_dense: ld (%d) must be >= d and a multiple of 4", j->ld);
-    GradParams p;
-    memset(&p, 0, sizeof(p));
-    for (int i = 0; i < j->n_segs; ++i) {
-        EH_REQUIRE(j->d_X[i] && j->d_y[i], "grad_dense: null segment %d", i);
-        EH_REQUIRE(((uintptr_t)j->d_X[i] % 16) == 0, "grad_dense: X must be 16-byte aligned");
-        p.seg_X[i] = j->d_X[i];
-        p.seg_y[i] = j->d_y[i];
-        p.coeff[i] = j->coeff[i];
-    }
-    p.beta = j->d_beta; p.out = j->d_out;
-    p.flag = j->d_flag; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
-    p.d = j->d; p.ld = j->ld;
-    p.rows_per_seg = j->rows_per_seg; p.n_segs = j->n_segs; p.model = j->model;
-    p.stamp = j->stamp; p.seq = next_launch_seq();
-    p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
-    cudaStream_t st = (cudaStream_t)stream;
-    if (j->ld > 8192) return launch_wide(p, d_scratch, scratch_bytes, st);
-    if (j->ld <= 1024) return launch_rowwarp(p, d_scratch, scratch_bytes, st);
-    if (j->ld <= 2048) return launch<2, 8>(j, p, d_scratch, scratch_bytes, st);
-    if (j->ld <= 4096) return launch<4, 4>(j, p, d_scratch, scratch_bytes, st);
-    return launch<8, 2>(j, p, d_scratch, scratch_bytes, st);
+    return eh::fill_and_launch(j, 1, d_scratch, scratch_bytes, stream);
+}
+
+extern "C" int eh_grad_dense_multi(const eh_grad_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes,
+                                   void* stream) {
+    return eh::fill_and_launch(jobs, n_jobs, d_scratch, scratch_bytes, stream);
 }
 
 // ------------------------------------------------------------------------------------------

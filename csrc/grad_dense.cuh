@@ -10,6 +10,8 @@ constexpr int GD_CONSUMERS = GD_CONSUMER_WARPS * 32;
 constexpr int GD_THREADS = GD_CONSUMERS + 32;
 constexpr int GD_MAX_STAGES = 8;
 constexpr int GD_MAX_SEGS = EH_MAX_SEGS;
+constexpr int GD_MAX_JOBS = 8;                 // messages batched into one launch
+constexpr int GD_TOTAL_SEGS = 32;              // partitions over all batched messages
 constexpr int GD_SMEM_BUDGET = 220 * 1024;
 
 struct GradScratchHdr {          // first 512 bytes of the scratch buffer
@@ -21,11 +23,19 @@ struct GradScratchHdr {          // first 512 bytes of the scratch buffer
 constexpr uint32_t DEC_GO = 1, DEC_SKIP = 2;
 
 struct GradParams {
-    const float* seg_X[EH_MAX_SEGS];
-    const float* seg_y[EH_MAX_SEGS];
+    const float* seg_X[GD_TOTAL_SEGS];
+    const float* seg_y[GD_TOTAL_SEGS];
     const float* beta;
-    float* out;
+    float* out;                      // single-message paths (wide fallback)
     uint32_t* flag;
+    // batched messages: job j owns CTAs [job_cta0[j], job_cta0[j+1]) and segments
+    // [job_seg0[j], job_seg0[j] + job_nsegs[j]) and writes job_out[j] / releases job_flag[j]
+    float* job_out[GD_MAX_JOBS];
+    uint32_t* job_flag[GD_MAX_JOBS];
+    int job_cta0[GD_MAX_JOBS + 1];
+    int job_seg0[GD_MAX_JOBS];
+    int job_nsegs[GD_MAX_JOBS];
+    int n_jobs;
     const uint32_t* beta_flag;
     uint32_t* err;
     GradScratchHdr* hdr;
@@ -37,8 +47,26 @@ struct GradParams {
     long long n_steps;
     uint32_t stamp, seq;
     unsigned long long timeout_ns;
-    float coeff[GD_MAX_SEGS];
+    float coeff[GD_TOTAL_SEGS];
 };
+
+// which batched message this CTA works for
+struct JobView {
+    int jb, b0, Gj, bl, seg0;
+    long long n_steps;
+};
+__device__ __forceinline__ JobView job_of_cta(const GradParams& p) {
+    JobView v;
+    int jb = 0;
+    while (jb + 1 < p.n_jobs && (int)blockIdx.x >= p.job_cta0[jb + 1]) ++jb;
+    v.jb = jb;
+    v.b0 = p.job_cta0[jb];
+    v.Gj = p.job_cta0[jb + 1] - v.b0;
+    v.bl = (int)blockIdx.x - v.b0;
+    v.seg0 = p.job_seg0[jb];
+    v.n_steps = (long long)p.steps_per_seg * p.job_nsegs[jb];
+    return v;
+}
 
 __device__ __forceinline__ float residual(int model, float p, float y) {
     if (model == EH_MODEL_LOGISTIC) {
@@ -55,7 +83,9 @@ __device__ __forceinline__ float residual(int model, float p, float y) {
 __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned char* smem_raw) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int G = gridDim.x, b = blockIdx.x;
+    const int G = gridDim.x;
+    const JobView jv = job_of_cta(p);
+    float* out = p.job_out[jv.jb];
     uint32_t gen = 0;
     grid_barrier(&p.hdr->barrier, gen);
 
@@ -63,11 +93,11 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
         const int ld4 = p.ld >> 2;
         const int n_groups = (ld4 + 31) / 32;                 // 32 float4 columns per group
         float4* sred = reinterpret_cast<float4*>(smem_raw);   // [8][32] float4, ring is idle now
-        for (int grp = b; grp < n_groups; grp += G) {
+        for (int grp = jv.bl; grp < n_groups; grp += jv.Gj) {
             const int c4 = grp * 32 + lane;
             float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
             if (c4 < ld4) {
-                for (int row = warp; row < G; row += GD_CONSUMER_WARPS) {
+                for (int row = jv.b0 + warp; row < jv.b0 + jv.Gj; row += GD_CONSUMER_WARPS) {
                     const float4 t = __ldcg(reinterpret_cast<const float4*>(p.partials + (size_t)row * p.ldp) + c4);
                     s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
                 }
@@ -83,11 +113,11 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
                 }
                 const int c = c4 * 4;
                 if (c + 3 < p.d) {
-                    *reinterpret_cast<float4*>(p.out + c) = t;
+                    *reinterpret_cast<float4*>(out + c) = t;
                 } else {
-                    if (c + 0 < p.d) p.out[c + 0] = t.x;
-                    if (c + 1 < p.d) p.out[c + 1] = t.y;
-                    if (c + 2 < p.d) p.out[c + 2] = t.z;
+                    if (c + 0 < p.d) out[c + 0] = t.x;
+                    if (c + 1 < p.d) out[c + 1] = t.y;
+                    if (c + 2 < p.d) out[c + 2] = t.z;
                 }
             }
             asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
@@ -102,7 +132,8 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
             p.hdr->barrier = 0;
             p.hdr->done = 0;
             __threadfence_system();
-            if (p.flag) st_release_sys(p.flag, p.stamp);
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_release_sys(p.job_flag[j], p.stamp);
         }
     }
 }
@@ -137,6 +168,8 @@ __device__ __forceinline__ uint32_t wait_for_parameters(const GradParams& p) {
 }
 
 // host-side launchers (defined next to their kernels)
+// CTA ranges of the batched messages, proportional to their tile counts (host)
+int assign_ctas(GradParams& p, int sm_count);
 int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
 int launch_wide(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
 

@@ -25,7 +25,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
     uint64_t* empty = full + GD_MAX_STAGES;
     __shared__ uint32_t s_decision;
 
-    const long long my_steps = (b < p.n_steps) ? (p.n_steps - b + G - 1) / G : 0;
+    const JobView jv = job_of_cta(p);
+    const long long my_steps = (jv.bl < jv.n_steps) ? (jv.n_steps - jv.bl + jv.Gj - 1) / jv.Gj : 0;
 
     if (tid == 0) {
         for (int s = 0; s < p.n_stages; ++s) {
@@ -42,8 +43,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
         long long issued = 0;
         uint64_t pol = l2_policy_evict_first();
         auto issue = [&](long long k) {
-            const long long step = b + k * G;
-            const int sg = (int)(step / p.steps_per_seg);
+            const long long step = jv.bl + k * (long long)jv.Gj;
+            const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
             const int row0 = (int)(step % p.steps_per_seg) * RB;
             const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
             const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
@@ -99,8 +100,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
         for (long long k = 0; k < my_steps; ++k) {
             const int st = (int)(k % p.n_stages);
             const uint32_t use = (uint32_t)(k / p.n_stages);
-            const long long step = b + k * G;
-            const int sg = (int)(step / p.steps_per_seg);
+            const long long step = jv.bl + k * (long long)jv.Gj;
+            const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
             const int row0 = (int)(step % p.steps_per_seg) * RB;
             const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
             const float cf = p.coeff[sg];
@@ -195,16 +196,13 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
     if (smem < 8 * 32 * sizeof(float4) + tail) smem = 8 * 32 * sizeof(float4) + tail;
     p.n_stages = stages;
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
-    p.n_steps = (long long)p.steps_per_seg * p.n_segs;
     auto kern = grad_dense_rowwarp_kernel<LPR, DVW>;
     static bool attr_done = false;
     if (!attr_done) {
         EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
         attr_done = true;
     }
-    long long grid = di.sm_count;
-    if (grid > p.n_steps) grid = p.n_steps;
-    if (grid < 1) grid = 1;
+    const int grid = assign_ctas(p, di.sm_count);
     p.ldp = p.ld;
     const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.ldp * sizeof(float);
     EH_REQUIRE(scratch_bytes >= need, "grad_dense: scratch too small (%zu < %zu)", scratch_bytes, need);

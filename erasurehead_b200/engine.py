@@ -241,8 +241,26 @@ class Engine:
 
     # ------------------------------------------------------------------ running
     def launches_per_round(self) -> int:
-        """Kernels this rank launches per round (gradient jobs + decoder on the root)."""
-        return self.n_jobs + (1 if self.ctx.is_root else 0) if self.on_gpu else 0
+        """Kernels this rank launches per round: gradient kernels (dense messages of one shape are
+        batched 8 messages / 32 partitions per launch by ``eh_run_rounds``) + the decoder on the root."""
+        if not self.on_gpu:
+            return 0
+        k = 0
+        if self.mc:
+            k = sum(2 * self._jobs[q].n_segs + 3 for q in range(self.n_jobs))
+        elif self.sparse:
+            k = self.n_jobs
+        else:
+            nb = segs = 0
+            for q in range(self.n_jobs):
+                ns = self._jobs[q].n_segs
+                if nb == 8 or segs + ns > 32:
+                    k += 1
+                    nb = segs = 0
+                nb += 1
+                segs += ns
+            k += 1 if nb else 0
+        return k + (1 if self.ctx.is_root else 0)
 
     def prepare(self) -> None:
         """Reset flags and publish the initial parameters (untimed set-up of a run)."""

@@ -128,6 +128,7 @@ def _declare(lib):
         "eh_ws_error": (i32, [P(WsLayout), vp, P(i32), vp]),
         "eh_grad_dense_scratch_bytes": (sz, [i32]),
         "eh_grad_dense": (i32, [P(GradJob), vp, sz, vp]),
+        "eh_grad_dense_multi": (i32, [P(GradJob), i32, vp, sz, vp]),
         "eh_grad_dense_noalloc_max_ld": (sz, []),
         "eh_grad_dense_noalloc": (i32, [P(GradJob), vp]),
         "eh_grad_mc_scratch_bytes": (sz, [i64, i32, i32]),

@@ -71,6 +71,13 @@ def launch_dense(job: GradJob, scratch: Scratch, stream: Optional[int] = None) -
                               stream_ptr() if stream is None else stream), "eh_grad_dense")
 
 
+def launch_dense_multi(jobs: Sequence[GradJob], scratch: Scratch, stream: Optional[int] = None) -> None:
+    """Up to 8 messages of one shape in a single launch (``eh_grad_dense_multi``)."""
+    arr = (GradJob * len(jobs))(*jobs)
+    check(lib().eh_grad_dense_multi(arr, len(jobs), scratch.ptr(), scratch.nbytes,
+                                    stream_ptr() if stream is None else stream), "eh_grad_dense_multi")
+
+
 def make_ell_job(idxs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], beta_ptr: int, out_ptr: int, d: int,
                  coeff: Sequence[float], model: int, bias_col: int = -1, stamp: int = 0, flag_ptr: int = 0,
                  beta_flag_ptr: int = 0, err_ptr: int = 0, timeout_ns: int = 0) -> GradEllJob:

@@ -103,6 +103,10 @@ typedef struct eh_grad_job {
 
 size_t eh_grad_dense_scratch_bytes(int d);
 int eh_grad_dense(const eh_grad_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
+/* Up to 8 messages of identical shape (same d, ld, rows_per_seg, model, parameters, stamp; at most 32
+ * partitions in total) in ONE launch: the CTAs are split between the messages, each message is
+ * reduced, shipped and flagged separately.  Used by the round loop for GPUs hosting several workers. */
+int eh_grad_dense_multi(const eh_grad_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes, void* stream);
 
 /* Same kernel for callers that cannot allocate device memory (fixed-latency loops that forbid
  * cudaMalloc after start-up, processes whose HBM is fully committed, plain C hosts without an
