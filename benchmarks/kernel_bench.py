@@ -109,6 +109,35 @@ def bench_eval(args, pk, src):
     return [rec, rec2]
 
 
+def bench_mc(args, pk, src):
+    """Multi-column (softmax) gradient: two tensor-core passes over X."""
+    from erasurehead_b200.ops import mc, synth
+    out = []
+    for rows, d, C_ in ((262144, 4096, 16), (1048576, 1024, 10), (2097152, 64, 7)):
+        X, _ = synth.synth_gmm(rows, d, 1, 0)
+        y = torch.randint(0, C_, (rows,), device="cuda").float()
+        Wp = mc.pack_params(torch.randn(d, C_, device="cuda") * 0.01)
+        G = torch.empty_like(Wp)
+        scr = mc.scratch(rows, d, C_, "cuda")
+        job = mc.make_job([X], [y], Wp.data_ptr(), G.data_ptr(), d, C_, [1.0], mc.MODEL_SOFTMAX)
+        med, mn = time_fn(lambda: mc.launch(job, scr), args.iters)
+        Xd = X[:, :d]
+        W = torch.randn(d, C_, device="cuda") * 0.01
+        def torch_ref():
+            S = torch.softmax(Xd @ W, 1)
+            S[torch.arange(rows, device="cuda"), y.long()] -= 1
+            return Xd.t() @ S
+        med2, _ = time_fn(torch_ref, max(3, args.iters // 2))
+        byt = rows * X.stride(0) * 4
+        rec = {"kernel": "grad_mc(tcgen05 fwd+bwd, softmax)", "rows": rows, "d": d, "C": C_, "ms": med, "ms_min": mn,
+               "X_passes": 2, "GBps_algorithmic(1 pass)": byt / med / 1e6,
+               "frac_of_hbm_" + src + "_at_2_passes": 2 * byt / med / 1e6 / pk["hbm_gbs"],
+               "torch_cublas_fp32_ms": med2, "speedup_vs_torch": med2 / med}
+        print(json.dumps(rec)); out.append(rec)
+        del X
+    return out
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=0)
@@ -125,5 +154,7 @@ if __name__ == "__main__":
         recs += bench_decoder(args)
     if args.only in ("", "eval"):
         recs += bench_eval(args, pk, src)
+    if args.only in ("", "mc"):
+        recs += bench_mc(args, pk, src)
     if args.out:
         json.dump(recs, open(args.out, "w"), indent=1)
