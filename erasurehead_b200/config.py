@@ -102,6 +102,7 @@ class RunConfig:
     metrics_jsonl: Optional[str] = None
     decode: str = "auto"                   # auto | table | solve
     quiet: bool = False
+    debug_poison: bool = False             # fill every message slot with NaN before a run (stale-read detector)
 
     def __post_init__(self):
         if self.update_rule not in ("GD", "AGD"):

@@ -268,6 +268,8 @@ class Engine:
             return
         from .ops import _lib
         self.ws.reset()
+        if self.cfg.debug_poison and self.ctx.is_root:
+            self._poison_slots()
         self.scratch.zero_()
         if self.dec is not None:
             self.t_decscratch.zero_()
@@ -277,6 +279,22 @@ class Engine:
             _lib.check(_lib.lib().eh_decoder_publish(C.byref(self.dec), self.first_round, _lib.stream_ptr()),
                        "eh_decoder_publish")
         self._cursor = self.first_round
+
+    def _poison_slots(self) -> None:
+        """Debug aid (compute-sanitizer is not available on every pool): NaN-fill all gradient slots
+        so that a decoder read of a slot no worker wrote in this run poisons the iterates, which
+        :meth:`finish` then reports."""
+        lay = self.ws.lay
+        n = int(lay.n_workers) * int(lay.n_msgs) * 2 * int(lay.d_pad)
+        self._tensor_from_ptr(self.ws.local + int(lay.off_slots), n).fill_(float("nan"))
+
+    def _tensor_from_ptr(self, ptr: int, n_floats: int):
+        """A float32 torch view of raw device memory owned by the workspace."""
+        class _Holder:
+            pass
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+        return self.torch.as_tensor(h, device=self.ctx.device)
 
     def enqueue(self, n_rounds: int) -> None:
         """Enqueue ``n_rounds`` further rounds on the current stream (no synchronisation)."""
@@ -328,6 +346,8 @@ class Engine:
         if any(errs):
             raise RuntimeError(f"device watchdog fired (per-rank error words {errs}); "
                                "a worker died or a stop rule became unsatisfiable")
+        if self.cfg.debug_poison and self.dec is not None and not bool(self.torch.isfinite(self.t_beta64).all()):
+            raise RuntimeError("debug_poison: the decoder consumed a slot that no worker wrote (stale read)")
 
     def run(self, rounds: Optional[int] = None) -> Optional[oracle.RunResult]:
         """Run ``rounds`` rounds (default: all remaining).  Returns the result on the root."""

@@ -172,3 +172,13 @@ def test_engine_softmax_multiclass_matches_oracle():
     ref2 = oracle.run_rounds(cfg2, build_scheme(cfg2, eng2.spec.B), data, eng2.delays, beta0=eng2.beta0, model=eng2.model)
     assert np.abs(r2.betaset - ref2.betaset).max() <= 1e-2 * max(1.0, np.abs(ref2.betaset).max())
     eng2.close()
+
+
+def test_debug_poison_mode_runs_clean():
+    """NaN-poisoned slots: a correct run never reads a slot nobody wrote (sanitizer substitute)."""
+    cfg = mk("approx", s=1, k=5, debug_poison=True)
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1)
+    eng = Engine(cfg, data, delays=spaced_delays(cfg.rounds, 8, seed=5))
+    res = eng.run()
+    assert np.all(np.isfinite(res.betaset))
+    eng.close()
