@@ -179,7 +179,7 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
                     solve_decode_row(D.d_B, n, s_S, k, M, s_a, lane);
                     for (int c = lane; c < k; c += 32) sc->a_coded[s_S[c]] = s_a[c];
                 }
-                done_mask = sel;    // messages beyond the first n-s are not used
+                // messages beyond the first n-s keep their arrival time but get weight 0
             } else {
                 const unsigned long long use = (D.decode == EH_DECODE_FIRST_PER_GROUP) ? first_mask : done_mask;
                 for (int w = lane; w < n; w += 32) sc->a_coded[w] = ((use >> w) & 1ull) ? 1.0 : 0.0;

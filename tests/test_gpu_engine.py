@@ -182,3 +182,48 @@ def test_debug_poison_mode_runs_clean():
     res = eng.run()
     assert np.all(np.isfinite(res.betaset))
     eng.close()
+
+
+@pytest.mark.parametrize("scheme,kw", [("coded", dict(n=30, s=3, seed=7)), ("approx", dict(n=30, s=2, k=15)),
+                                       ("replication", dict(n=30, s=4)), ("avoidstragg", dict(n=30, s=3)),
+                                       ("partial_coded", dict(n=12, s=2, P=5, rows=36 * 40, seed=5))])
+def test_reference_cluster_sizes_30_workers(scheme, kw):
+    """The reference's default cluster is 30 workers (run_approx_coding.sh:2): the decode table has
+    C(30,3) = 4060 rows and cond(B) reaches 1e5 -- float64 decode on the device."""
+    rows = kw.pop("rows", 30 * 64)
+    cfg = mk(scheme, rows=rows, d=40, rounds=5, **kw)
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=2)
+    dl = spaced_delays(cfg.rounds, cfg.n_workers, seed=11, gap=1e-3)
+    eng = Engine(cfg, data, delays=dl)
+    res = eng.run()
+    ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0)
+    scale = max(1.0, np.abs(ref.betaset).max())
+    # messages are fp32 and |decode weights| reach ~1e2-1e4 for (30,3): tolerance scales with them
+    tol = 5e-4 * max(1.0, np.abs(ref.weights).max())
+    assert np.abs(res.betaset - ref.betaset).max() <= tol * scale
+    assert np.array_equal(res.n_collected, ref.n_collected)
+    assert np.array_equal(res.worker_timeset >= 0, ref.worker_timeset >= 0)
+    eng.close()
+
+
+def test_random_scheme_configurations_match_oracle():
+    """Randomised (n, s, k, P) sweep of the device decoder against the oracle."""
+    rng = np.random.RandomState(123)
+    for trial in range(10):
+        scheme = ["naive", "coded", "replication", "avoidstragg", "approx", "partial_coded", "partial_replication"][trial % 7]
+        s = int(rng.randint(1, 4)) if scheme != "naive" else 0
+        groups = int(rng.randint(2, 5))
+        n = groups * (s + 1)
+        P = s + 1 + int(rng.randint(1, 3)) if scheme.startswith("partial") else 0
+        k = int(rng.randint(1, n + 1))
+        parts = (P - s) * n if P else n
+        cfg = mk(scheme, n=n, s=s, P=P, k=k, rows=parts * 48, d=24, rounds=4, seed=trial, rule=("GD" if trial % 2 else "AGD"))
+        data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=trial)
+        dl = spaced_delays(cfg.rounds, n, seed=trial, gap=1e-3)
+        eng = Engine(cfg, data, delays=dl)
+        res = eng.run()
+        ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0)
+        tol = 5e-4 * max(1.0, np.abs(ref.weights).max()) * max(1.0, np.abs(ref.betaset).max())
+        assert np.abs(res.betaset - ref.betaset).max() <= tol, (scheme, n, s, k, P)
+        assert np.array_equal(res.n_collected, ref.n_collected), (scheme, n, s, k, P)
+        eng.close()

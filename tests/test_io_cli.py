@@ -115,3 +115,16 @@ def test_checkpoint_resume_cpu(tmp_path):
     res2 = eng2.run()
     assert np.allclose(res2.betaset, full.betaset[4:], atol=1e-12)
     assert np.allclose(res2.timeset, full.timeset[4:])
+
+
+def test_metrics_jsonl_and_npy_outputs(tmp_path):
+    import json
+    generate_gmm_to_disk(9, 800, 6, str(tmp_path), 1, 0, 0, seed=1)
+    mj = str(tmp_path / "m.jsonl")
+    out = cli.run(parse_argv(f"9 800 6 {tmp_path} 0 x 1 1 0 3 5 1 AGD --rounds=5 --gpus=-1 --quiet --metrics-jsonl={mj}".split()))
+    recs = [json.loads(l) for l in open(mj)]
+    assert len(recs) == 5 and {"round", "time_s", "n_collected", "arrived_mask", "weights", "train_loss", "auc"} <= set(recs[0])
+    assert bin(recs[0]["arrived_mask"]).count("1") == recs[0]["n_collected"]
+    rd = out["results_dir"]
+    for suffix in ("betaset", "timeset", "worker_timeset", "training_loss", "testing_loss", "auc"):
+        assert os.path.exists(f"{rd}approx_acc_1_5_{suffix}.npy")
