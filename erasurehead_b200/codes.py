@@ -37,6 +37,9 @@ __all__ = [
     "frc_group",
     "frc_members",
     "binomial_table",
+    "unique_rows",
+    "compare_masks",
+    "find_mask_row",
 ]
 
 
@@ -143,3 +146,31 @@ def frc_members(n: int, s: int) -> np.ndarray:
     if n % (s + 1):
         raise ValueError("n_workers must be a multiple of n_stragglers+1")
     return np.arange(n).reshape(n // (s + 1), s + 1)
+
+
+# ---- small helpers the reference keeps next to getA (util.py:58-62,105-123); unused by its drivers
+# but part of its utility surface, so equivalents are provided.
+
+def unique_rows(a: np.ndarray) -> np.ndarray:
+    """Distinct rows of a 2-D array, sorted lexicographically (``unique_rows``, util.py:58-62)."""
+    return np.unique(np.ascontiguousarray(a), axis=0)
+
+
+def compare_masks(a: Sequence[bool], b: Sequence[bool]) -> int:
+    """Lexicographic order used by the reference's decode-table search (``compare``, util.py:105-111):
+    +1 if the first differing position is set in ``a`` only, -1 if in ``b`` only, 0 if equal."""
+    for x, y in zip(a, b):
+        if x and not y:
+            return 1
+        if y and not x:
+            return -1
+    return 0
+
+
+def find_mask_row(table: np.ndarray, mask: Sequence[bool]) -> int:
+    """Row index of ``mask`` in a completed-mask table ordered like ``decode_table`` -- the job of
+    ``binary_search_row_wise`` (util.py:113-123), done with the closed-form combinadic rank."""
+    r = mask_rank(mask)
+    if r >= len(table) or not np.array_equal(np.asarray(table[r], dtype=bool), np.asarray(mask, dtype=bool)):
+        raise KeyError("mask not in table")
+    return r

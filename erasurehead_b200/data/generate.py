@@ -22,6 +22,16 @@ def _gmm_block(rng, mu1, mu2, rows, d):
                            mfac * rng.standard_normal((c2, d)) + mu2))
 
 
+def generate_random_matrix_normal(mu1, mu2, n_rows, n_cols, rng=None):
+    """Two-component GMM block with identity covariance scaled by 10/sqrt(d) (util.py:39-43)."""
+    return _gmm_block(rng or np.random, np.asarray(mu1), np.asarray(mu2), n_rows, n_cols)
+
+
+def generate_random_binvec(n, rng=None):
+    """Random +-1 vector (util.py:46-47)."""
+    return (rng or np.random).randint(2, size=n) * 2 - 1
+
+
 def _labels(rng, X, beta_star, task, classes=1):
     if task == "linear":
         return X.dot(beta_star) / np.sqrt(len(beta_star)) + 0.1 * rng.standard_normal(X.shape[0])

@@ -71,3 +71,18 @@ def test_frc_members():
     assert m.shape == (4, 2) and codes.frc_group(5, 1) == 2
     with pytest.raises(ValueError):
         codes.frc_members(7, 1)
+
+
+def test_reference_utility_helpers():
+    a = np.array([[1, 0], [0, 1], [1, 0]])
+    assert codes.unique_rows(a).tolist() == [[0, 1], [1, 0]]
+    assert codes.compare_masks([1, 0, 1], [1, 1, 0]) == -1 and codes.compare_masks([1, 1], [1, 1]) == 0
+    n, s = 6, 2
+    table = np.array([codes.unrank_mask(r, n, s) for r in range(15)])
+    for r in range(15):
+        assert codes.find_mask_row(table, table[r]) == r
+    from erasurehead_b200.data.generate import generate_random_binvec, generate_random_matrix_normal
+    v = generate_random_binvec(50, np.random.RandomState(0))
+    assert set(np.unique(v)) <= {-1, 1}
+    m = generate_random_matrix_normal(np.ones(4), -np.ones(4), 100, 4, np.random.RandomState(0))
+    assert m.shape == (100, 4)
