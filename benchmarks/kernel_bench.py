@@ -109,6 +109,38 @@ def bench_eval(args, pk, src):
     return [rec, rec2]
 
 
+def bench_ell(args, pk, src):
+    """One-hot gradient at the reference's real-dataset shapes (synthetic data of that shape)."""
+    from erasurehead_b200.data import generate_onehot, DATASET_SHAPES
+    from erasurehead_b200.ops import grad
+    out = []
+    for name, sh in DATASET_SHAPES.items():
+        ds = generate_onehot(sh["n_rows"], sh["n_cols"], sh["nnz"], 1, seed=1, task=sh["task"])
+        idx = torch.from_numpy(ds.ell(0)).cuda()
+        y = torch.tensor(ds.labels(0), dtype=torch.float32, device="cuda")
+        d = sh["n_cols"]
+        beta = torch.randn(d, device="cuda") * 0.1
+        sc = grad.ell_scratch(d, "cuda")
+        o = torch.empty(d, device="cuda")
+        model = 1 if sh["task"] == "linear" else 0
+        med, mn = time_fn(lambda: grad.grad_ell(idx, y, beta, model=model, bias_col=d - 1, scratch=sc, out=o), args.iters)
+        Xs = torch.sparse_csr_tensor(torch.arange(0, idx.numel() + 1, idx.shape[1], device="cuda", dtype=torch.int64),
+                                     idx.reshape(-1).long(), torch.ones(idx.numel(), device="cuda"), size=(idx.shape[0], d))
+        def torch_ref():
+            p = torch.mv(Xs, beta)
+            r = -y / (torch.exp(p * y) + 1) if model == 0 else -2 * (y - p)
+            return torch.mv(Xs.t(), r) if False else torch.sparse.mm(Xs.t(), r[:, None])
+        try:
+            med2, _ = time_fn(torch_ref, 3)
+        except Exception:
+            med2 = None
+        byt = idx.numel() * 4 + idx.shape[0] * 4 + 3 * d * 4
+        rec = {"kernel": "grad_ell", "shape": name, "rows": idx.shape[0], "d": d, "nnz": idx.shape[1], "ms": med,
+               "ms_min": mn, "index_GBps": byt / med / 1e6, "torch_sparse_csr_ms": med2}
+        print(json.dumps(rec)); out.append(rec)
+    return out
+
+
 def bench_mc(args, pk, src):
     """Multi-column (softmax) gradient: two tensor-core passes over X."""
     from erasurehead_b200.ops import mc, synth
@@ -154,6 +186,8 @@ if __name__ == "__main__":
         recs += bench_decoder(args)
     if args.only in ("", "eval"):
         recs += bench_eval(args, pk, src)
+    if args.only in ("", "ell"):
+        recs += bench_ell(args, pk, src)
     if args.only in ("", "mc"):
         recs += bench_mc(args, pk, src)
     if args.out:

@@ -9,6 +9,8 @@
 // registers and added once per warp instead of `rows` colliding atomics.  The accumulation
 // vector lives in `scratch`, zeroed and shipped (to local or peer memory + release flag) by
 // the same cooperative kernel.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace eh {
@@ -127,10 +129,159 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
 }
 
 
+// ---------------------------------------------------------------------------------------------
+// Shared-memory variant for feature spaces that fit on chip (d <= ~56K, i.e. Covertype- and
+// KC-House-shaped data): every CTA keeps a private copy of the gradient (and, if it also fits, of
+// the parameters) in shared memory, so the 44-55 scatter-adds per row are shared-memory atomics
+// instead of L2 atomics that pile up on the popular one-hot columns.  The per-CTA gradients are then
+// combined through scratch in a fixed order like the dense kernel (bitwise reproducible).
+// ---------------------------------------------------------------------------------------------
+constexpr int GES_THREADS = 512;
+
+template <bool BETA_IN_SMEM>
+__global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const EllParams p, float* __restrict__ partials) {
+    extern __shared__ __align__(16) float ges_smem[];
+    float* acc = ges_smem;
+    float* bsm = ges_smem + ((p.d + 3) & ~3);
+    __shared__ uint32_t s_code;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int G = gridDim.x, b = blockIdx.x;
+
+    for (int c = tid; c < p.d; c += GES_THREADS) acc[c] = 0.f;
+
+    if (tid == 0) {
+        uint32_t code = GE_GO;
+        if (b == 0) {
+            if (p.beta_flag) {
+                const uint64_t t0 = globaltimer();
+                while (true) {
+                    const uint32_t f = ld_acquire_sys(p.beta_flag);
+                    if (f == p.stamp) break;
+                    if (f > p.stamp) { code = GE_SKIP; break; }
+                    if (p.err && ld_acquire_sys(p.err) != 0) { code = GE_SKIP; break; }
+                    if (globaltimer() - t0 > p.timeout_ns) {
+                        if (p.err) atomicCAS(p.err, 0u, (uint32_t)(-EH_ETIMEOUT));
+                        code = GE_SKIP;
+                        break;
+                    }
+                    nanosleep(64);
+                }
+            }
+            st_release_gpu(&p.hdr->decision, (p.seq << 2) | code);
+        } else {
+            uint32_t v;
+            while (((v = ld_acquire_gpu(&p.hdr->decision)) >> 2) != p.seq) nanosleep(32);
+            code = v & 3u;
+        }
+        s_code = code;
+    }
+    __syncthreads();
+    if (s_code == GE_SKIP) return;
+
+    if (BETA_IN_SMEM) {
+        for (int c = tid; c < p.d; c += GES_THREADS) bsm[c] = __ldcg(p.beta + c);
+        __syncthreads();
+    }
+
+    const long long gwarp = (long long)b * (GES_THREADS / 32) + warp;
+    const long long nwarps = (long long)G * (GES_THREADS / 32);
+    float bias_acc = 0.f;
+    constexpr int RW = 4;                      // rows in flight per warp: hides the index-load latency
+    for (long long row0 = gwarp * RW; row0 < p.rows; row0 += nwarps * RW) {
+        int cols[RW][2];
+        float yv[RW], cf[RW], s[RW];
+        const int32_t* rip[RW];
+#pragma unroll
+        for (int r = 0; r < RW; ++r) {
+            const long long row = row0 + r;
+            const bool valid = row < p.rows;
+            const int sg = valid ? (int)(row / p.rows_per_seg) : 0;
+            const int lr = valid ? (int)(row % p.rows_per_seg) : 0;
+            rip[r] = p.seg_idx[sg] + (size_t)lr * p.nnz;
+            cols[r][0] = (valid && lane < p.nnz) ? __ldg(rip[r] + lane) : -1;
+            cols[r][1] = (valid && lane + 32 < p.nnz) ? __ldg(rip[r] + lane + 32) : -1;
+            yv[r] = valid ? __ldg(p.seg_y[sg] + lr) : 0.f;
+            cf[r] = valid ? p.coeff[sg] : 0.f;
+        }
+#pragma unroll
+        for (int r = 0; r < RW; ++r) {
+            float t = 0.f;
+            if (cols[r][0] >= 0) t += BETA_IN_SMEM ? bsm[cols[r][0]] : __ldcg(p.beta + cols[r][0]);
+            if (cols[r][1] >= 0) t += BETA_IN_SMEM ? bsm[cols[r][1]] : __ldcg(p.beta + cols[r][1]);
+            if (p.nnz > 64 && row0 + r < p.rows)
+                for (int k = lane + 64; k < p.nnz; k += 32) {
+                    const int c = __ldg(rip[r] + k);
+                    t += BETA_IN_SMEM ? bsm[c] : __ldcg(p.beta + c);
+                }
+            s[r] = t;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int r = 0; r < RW; ++r) s[r] += __shfl_xor_sync(0xffffffffu, s[r], o);
+        }
+#pragma unroll
+        for (int r = 0; r < RW; ++r) {
+            const float rs = cf[r] * ell_residual(p.model, s[r], yv[r]);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                if (cols[r][q] >= 0) {
+                    if (cols[r][q] == p.bias_col) bias_acc += rs;
+                    else atomicAdd(acc + cols[r][q], rs);
+                }
+            }
+            if (p.nnz > 64 && row0 + r < p.rows)
+                for (int k = lane + 64; k < p.nnz; k += 32) {
+                    const int c = __ldg(rip[r] + k);
+                    if (c == p.bias_col) bias_acc += rs;
+                    else atomicAdd(acc + c, rs);
+                }
+        }
+    }
+    if (p.bias_col >= 0) {
+        bias_acc = warp_sum(bias_acc);
+        if (lane == 0 && bias_acc != 0.f) atomicAdd(acc + p.bias_col, bias_acc);
+    }
+    __syncthreads();
+    float* mine = partials + (size_t)b * p.d;
+    for (int c = tid; c < p.d; c += GES_THREADS) __stcg(mine + c, acc[c]);
+
+    uint32_t gen = 0;
+    grid_barrier(&p.hdr->barrier, gen);
+
+    // ordered reduction: CTA b owns a contiguous column range
+    const int chunk = (p.d + G - 1) / G;
+    const int c0 = b * chunk, c1 = min(p.d, c0 + chunk);
+    for (int c = c0 + tid; c < c1; c += GES_THREADS) {
+        float t = 0.f;
+        for (int g = 0; g < G; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
+        p.out[c] = t;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence_system();
+        const uint32_t old = atom_add_acq_rel_gpu(&p.hdr->done, 1u);
+        if (old == (uint32_t)G - 1) {
+            p.hdr->barrier = 0;
+            p.hdr->done = 0;
+            __threadfence_system();
+            if (p.flag) st_release_sys(p.flag, p.stamp);
+        }
+    }
+}
+
+constexpr size_t GES_SMEM_LIMIT = 224 * 1024;
+
 }  // namespace eh
 
 extern "C" size_t eh_grad_ell_scratch_bytes(int d) {
-    return sizeof(eh::EllScratchHdr) + (size_t)(d + 32) * sizeof(float);
+    size_t b = sizeof(eh::EllScratchHdr) + (size_t)(d + 32) * sizeof(float);
+    if ((size_t)(d + 4) * sizeof(float) <= eh::GES_SMEM_LIMIT) {      // shared-memory variant: per-CTA partials
+        int sm = eh::dev_info().sm_count;
+        if (sm <= 0) sm = 160;
+        b = sizeof(eh::EllScratchHdr) + (size_t)sm * (size_t)d * sizeof(float) + 256;
+    }
+    return b;
 }
 
 extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
@@ -156,6 +307,27 @@ extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scr
     p.model = j->model; p.bias_col = j->bias_col; p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     const DevInfo& di = dev_info();
+    const size_t acc_bytes = (size_t)((j->d + 3) & ~3) * sizeof(float);
+    if (acc_bytes <= GES_SMEM_LIMIT && getenv("EH_ELL_GLOBAL") == nullptr) {
+        // shared-memory variant
+        const bool both = 2 * acc_bytes <= GES_SMEM_LIMIT;
+        const size_t smem = both ? 2 * acc_bytes : acc_bytes;
+        long long grid = di.sm_count;
+        const long long want = (p.rows * 32 + GES_THREADS - 1) / GES_THREADS;
+        if (grid > want) grid = want;
+        if (grid < 1) grid = 1;
+        float* partials = p.gacc;
+        EH_REQUIRE(scratch_bytes >= sizeof(EllScratchHdr) + (size_t)grid * j->d * sizeof(float),
+                   "grad_ell: scratch too small for the shared-memory variant");
+        const void* kern = both ? (const void*)grad_ell_smem_kernel<true> : (const void*)grad_ell_smem_kernel<false>;
+        static bool attr_done[2] = {false, false};
+        if (!attr_done[both]) {
+            EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GES_SMEM_LIMIT));
+            attr_done[both] = true;
+        }
+        void* args[] = {(void*)&p, (void*)&partials};
+        return launch_grid_sync(kern, dim3((unsigned)grid), dim3(GES_THREADS), args, smem, (cudaStream_t)stream);
+    }
     int occ = 0;
     EH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, grad_ell_kernel, GE_THREADS, 0));
     if (occ > 4) occ = 4;
