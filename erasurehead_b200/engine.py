@@ -252,13 +252,17 @@ class Engine:
             k = self.n_jobs
         else:
             nb = segs = 0
+            big_prev = False
             for q in range(self.n_jobs):
-                ns = self._jobs[q].n_segs
-                if nb == 8 or segs + ns > 32:
+                j = self._jobs[q]
+                ns = j.n_segs
+                big = ns * j.rows_per_seg * j.ld_or_nnz * 4 > (16 << 20)       # same rule as csrc/engine.cu
+                if nb and (big or big_prev or nb == 8 or segs + ns > 32):
                     k += 1
                     nb = segs = 0
                 nb += 1
                 segs += ns
+                big_prev = big
             k += 1 if nb else 0
         return k + (1 if self.ctx.is_root else 0)
 
