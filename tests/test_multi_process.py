@@ -7,7 +7,8 @@ import sys
 import pytest
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ALL = ["naive", "coded", "replication", "avoidstragg", "approx", "partial_coded", "partial_replication", "sparse"]
+ALL = ["naive", "coded", "replication", "avoidstragg", "approx", "partial_coded", "partial_replication", "sparse",
+       "softmax"]
 
 
 def _free_port():
@@ -26,9 +27,9 @@ def _torchrun(nproc, device, schemes, timeout=300):
 
 
 def test_two_process_gloo_cpu():
-    rc, out = _torchrun(2, "cpu", ["approx", "coded", "partial_coded"])
+    rc, out = _torchrun(2, "cpu", ["approx", "coded", "partial_coded", "softmax"])
     assert rc == 0, out[-3000:]
-    assert out.count("OK") == 3
+    assert out.count("OK") == 4
 
 
 def _gpu_count():
