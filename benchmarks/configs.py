@@ -28,7 +28,7 @@ import torch  # noqa: E402
 
 from erasurehead_b200 import Engine, RunConfig, triple_from_scheme  # noqa: E402
 from erasurehead_b200.data import generate_gmm, generate_onehot  # noqa: E402
-from erasurehead_b200.delays import delay_table, expected_kth_wait  # noqa: E402
+from erasurehead_b200.delays import expected_kth_wait  # noqa: E402
 from erasurehead_b200.parallel.context import init_distributed  # noqa: E402
 
 OUT = []

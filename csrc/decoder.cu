@@ -81,14 +81,16 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
         bool aborted = false;
         bool stop = (cnt_priv >= D.need_private) && (cnt_coded >= D.need_count || cnt_groups >= D.need_groups);
         uint32_t idle = 0;
+        bool drain = false;     // a message was just consumed: others may be ready too, skip the flag sweep
         while (!stop) {
             const uint64_t now = globaltimer();
-            // poll the flags of entries still waiting
+            // poll the flags of entries still waiting (a message seen later can never be ready earlier
+            // than one that is ready now, so draining the ready set first keeps the arrival order)
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
 #pragma unroll
                 for (int m = 0; m < EH_MAX_MSGS; ++m) {
-                    if (ent[q][m].state == 0) {
+                    if (!drain && ent[q][m].state == 0) {
                         const uint32_t f = ld_acquire_sys(ws_flag(ws0, D.lay, lane + 32 * q, m));
                         if (f == stamp) {
                             ent[q][m].state = 1;
@@ -121,6 +123,7 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
             }
             if (best != NEVER) {
                 idle = 0;
+                drain = true;
                 const int w = (int)(bkey & 0xffffu);
                 const int m = (bkey >> 16) ? EH_MSG_CODED : EH_MSG_PRIVATE;
 #pragma unroll
@@ -150,6 +153,7 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
                 continue;
             }
             // nothing ready: watchdog + back-off
+            if (drain) { drain = false; continue; }
             const uint64_t limit = D.timeout_ns ? D.timeout_ns : 60ull * 1000000000ull;
             uint32_t e = 0;
             if (lane == 0) {

@@ -17,8 +17,8 @@ overridable: ``--rounds``, ``--alpha``, ``--lr-schedule={const,t0decay,expdecay}
 from __future__ import annotations
 
 import dataclasses
-from dataclasses import dataclass, field
-from typing import List, Optional, Sequence
+from dataclasses import dataclass
+from typing import Optional, Sequence
 
 import numpy as np
 

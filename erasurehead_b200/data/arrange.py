@@ -24,7 +24,6 @@ from typing import Optional, Tuple
 
 import numpy as np
 
-from ..utils import io
 from .dataset import Dataset, ell_to_csr
 
 AMAZON_SKIP_PAIRS = ((5, 7), (2, 3))          # util.py:52

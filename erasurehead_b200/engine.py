@@ -18,7 +18,7 @@ import ctypes as C
 import json
 import time
 from math import comb
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import numpy as np
 

@@ -12,7 +12,7 @@ from typing import Optional, Sequence
 import torch
 
 from . import _lib
-from ._lib import GradEllJob, GradJob, check, lib, ptr, stream_ptr
+from ._lib import GradEllJob, GradJob, check, lib, stream_ptr
 
 
 class Scratch:
@@ -42,7 +42,7 @@ def _segments(job, Xs, ys, coeff):
     if not (1 <= n <= _lib.EH_MAX_SEGS) or len(ys) != n or len(coeff) != n:
         raise ValueError(f"need 1..{_lib.EH_MAX_SEGS} segments with matching labels/coefficients")
     for i in range(n):
-        job.d_X[i] = Xs[i].data_ptr() if hasattr(job, "d_X") else 0
+        job.d_X[i] = Xs[i].data_ptr()
         job.d_y[i] = ys[i].data_ptr()
         job.coeff[i] = float(coeff[i])
     job.n_segs = n

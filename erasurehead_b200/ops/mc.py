@@ -9,7 +9,6 @@ from typing import Optional, Sequence
 
 import torch
 
-from . import _lib
 from ._lib import McJob, check, lib, stream_ptr
 
 MODEL_SOFTMAX = 2

@@ -13,15 +13,14 @@ path is testable without a GPU.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
-from typing import List, Optional
+from dataclasses import dataclass
+from typing import Optional
 
 import numpy as np
 
 from . import codes
 from .models import Model, get_model
-from .schemes import (DECODE_FIRST_PER_GROUP, DECODE_LSTSQ, DECODE_SUM, MSG_CODED, MSG_PRIVATE,
-                      SchemeSpec)
+from .schemes import DECODE_FIRST_PER_GROUP, DECODE_SUM, MSG_CODED, MSG_PRIVATE, SchemeSpec
 
 __all__ = ["RunResult", "gd_update", "agd_update", "worker_messages", "plan_round", "run_rounds", "initial_beta"]
 
@@ -57,8 +56,9 @@ def initial_beta(spec: SchemeSpec, d: int, seed: Optional[int], n_out: int = 1) 
     shape = (d,) if n_out == 1 else (d, n_out)
     if spec.beta0 == "zeros":
         return np.zeros(shape)
-    rng = np.random if seed is None else np.random.RandomState(seed + 7919)
-    return rng.standard_normal(shape) if seed is not None else np.random.randn(*shape)
+    if seed is None:
+        return np.random.randn(*shape)               # unseeded like the reference (naive.py:23)
+    return np.random.RandomState(seed + 7919).standard_normal(shape)
 
 
 def worker_messages(model: Model, spec: SchemeSpec, data, w: int, beta: np.ndarray):

@@ -47,7 +47,6 @@ class NcclBaselineEngine:
         self.beta32 = self.beta.float()
         self.eta = cfg.learning_rates()
         # every rank sends the same number of message rows (pad with zeros) so gather is regular
-        self.per_rank = max(len(self.ctx.local_workers(n)) for _ in [0])
         counts = [len([w for w in range(n) if w % self.ctx.world == r]) for r in range(self.ctx.world)]
         self.max_local = max(counts)
         self.sendbuf = torch.zeros((self.max_local, spec.n_msgs, d), dtype=torch.float32, device=dev)

@@ -32,7 +32,7 @@ approximate_coding.py:144, partial_coded.py:174, partial_replication.py:166).
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import List, Optional
 
 import numpy as np
