@@ -281,13 +281,13 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
         const uint32_t old = atom_add_acq_rel_gpu(&sc->done, 1u);
         if (old == gridDim.x - 1) {
             sc->done = 0;
-            __threadfence_system();
             const uint64_t now = globaltimer();
             if (!aborted) {
                 if (D.d_timeset) D.d_timeset[r] = (double)(now - t_start) * 1e-9;
                 *D.d_tstart = now;
+                __threadfence_system();
                 for (int pe = 0; pe < D.n_peers; ++pe)
-                    st_release_sys(ws_beta_flag(D.d_ws_peer[pe], D.lay), stamp + 1u);
+                    st_relaxed_sys(ws_beta_flag(D.d_ws_peer[pe], D.lay), stamp + 1u);   // one fence, n_peers stores
             }
         }
     }

@@ -133,7 +133,7 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
             p.hdr->done = 0;
             __threadfence_system();
             for (int j = 0; j < p.n_jobs; ++j)
-                if (p.job_flag[j]) st_release_sys(p.job_flag[j], p.stamp);
+                if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);      // ordered by the fence above
         }
     }
 }
