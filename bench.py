@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--scheme", default="approx")
     ap.add_argument("--delay-scale", type=float, default=DELAY_SCALE)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"], help="feature storage (headline: fp32)")
     return ap.parse_args()
 
 
@@ -124,7 +125,7 @@ def main():
     ic, pp, cv = triple_from_scheme(args.scheme)
     n_rows = n * args.rows
     cfg = RunConfig(n + 1, n_rows, args.cols, "", 0, "x", ic, s, pp, cv, k, 1, "AGD", rounds=2 * (W + K) + 2,
-                    synthetic=True, seed=1, delay_scale=args.delay_scale, quiet=True)
+                    synthetic=True, seed=1, delay_scale=args.delay_scale, quiet=True, dtype=args.dtype)
     if args.impl == "nccl":
         from erasurehead_b200.parallel.nccl_baseline import NcclBaselineEngine as Eng
     else:
@@ -176,11 +177,11 @@ def main():
         torch.distributed.all_reduce(lt)
     if ctx.is_root:
         value = n_rows * K / (ms * 1e-3)
-        hbm_bytes = eng.launches_per_round() and (args.workers_per_gpu * (s + 1) * args.rows * args.cols * 4)
+        hbm_bytes = args.workers_per_gpu * (s + 1) * args.rows * args.cols * (2 if args.dtype == "bf16" else 4)
         out = {
             "metric": "agc_train_samples_per_sec_injected_stragglers", "value": value, "unit": "samples/s",
             "n_gpus": N, "steps": K, "warmup": W, "ms_per_step": ms / K, "iters_per_sec": K / (ms * 1e-3),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.dtype,
             "data": "synthetic (device-generated GMM, generate_data.py distribution), random-init weights",
             "impl": args.impl,
             "config": {"model": "logistic_regression", "scheme": cfg.scheme, "n_workers": n, "n_stragglers": s,

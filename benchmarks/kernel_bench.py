@@ -61,6 +61,15 @@ def bench_grad(args, pk, src):
                "frac_of_hbm_" + src: byt / med / 1e6 / pk["hbm_gbs"], "torch_two_pass_ms": med2,
                "speedup_vs_two_pass": med2 / med}
         print(json.dumps(rec)); out.append(rec)
+        if d >= 2048:
+            Xb = X.to(torch.bfloat16)
+            medb, mnb = time_fn(lambda: grad.grad_dense(Xb, y, beta, d=d, scratch=sc, out=o), args.iters)
+            bytb = rows * Xb.stride(0) * 2
+            recb = {"kernel": "grad_dense(bf16 rows)", "rows": rows, "d": d, "ms": medb, "ms_min": mnb,
+                    "GBps": bytb / medb / 1e6, "frac_of_hbm_" + src: bytb / medb / 1e6 / pk["hbm_gbs"],
+                    "rows_per_s_vs_fp32": med / medb}
+            print(json.dumps(recb)); out.append(recb)
+            del Xb
         del X, y
     return out
 

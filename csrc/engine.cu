@@ -52,25 +52,26 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.ldw = (wj.d + 31) / 32 * 32; j.C = wj.classes; j.model = wj.model; j.stamp = stamp;
                 j.timeout_ns = plan->timeout_ns;
                 rc = eh_grad_mc(&j, plan->d_scratch, plan->scratch_bytes, stream);
-            } else if (!wj.sparse) {
+            } else if (!wj.sparse || wj.sparse == 3) {
                 eh_grad_job j;
                 memset(&j, 0, sizeof(j));
                 for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
-                    j.d_X[i] = (const float*)wj.d_X[i];
+                    j.d_X[i] = wj.d_X[i];
                     j.d_y[i] = wj.d_y[i];
                     j.coeff[i] = wj.coeff[i];
                 }
                 j.d_beta = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.ld = wj.ld_or_nnz;
                 j.model = wj.model; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
+                j.x_bf16 = (wj.sparse == 3);
                 // batching pays for latency-bound messages; a bandwidth-bound message (> 16 MB of X) gets
                 // its own launch so that it ships as soon as it is done instead of with the slowest one
-                const size_t job_bytes = (size_t)j.n_segs * j.rows_per_seg * j.ld * sizeof(float);
+                const size_t job_bytes = (size_t)j.n_segs * j.rows_per_seg * j.ld * (j.x_bf16 ? 2 : 4);
                 const bool small = job_bytes <= ((size_t)16 << 20);
                 const bool fits = small && nb < 8 && nb_segs + j.n_segs <= 32 &&
                                   (nb == 0 || (batch[0].d == j.d && batch[0].ld == j.ld &&
                                                batch[0].rows_per_seg == j.rows_per_seg && batch[0].model == j.model &&
-                                               (size_t)batch[0].n_segs * batch[0].rows_per_seg * batch[0].ld * sizeof(float) <=
+                                               batch[0].x_bf16 == j.x_bf16 && (size_t)batch[0].n_segs * batch[0].rows_per_seg * batch[0].ld * sizeof(float) <=
                                                    ((size_t)16 << 20)));
                 if (!fits) {
                     rc = flush();

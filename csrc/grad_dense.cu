@@ -23,14 +23,29 @@
 
 namespace eh {
 
-template <int DV, int RB>
+// 16 bytes of a row as E floats: 4 fp32 values, or 8 bf16 values widened to fp32
+template <int E>
+__device__ __forceinline__ void unpack16(const uint4& q, float (&f)[E]) {
+    if constexpr (E == 4) {
+        f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y); f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w);
+    } else {
+        f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
+        f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
+        f[4] = __uint_as_float(q.z << 16); f[5] = __uint_as_float(q.z & 0xffff0000u);
+        f[6] = __uint_as_float(q.w << 16); f[7] = __uint_as_float(q.w & 0xffff0000u);
+    }
+}
+
+// E = elements per 16-byte vector: 4 (fp32 rows) or 8 (bf16 rows); DV vectors per thread; RB rows per tile
+template <int E, int DV, int RB>
 __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int EB = 16 / E;                         // bytes per element
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int G = gridDim.x, b = blockIdx.x;
-    const uint32_t stage_bytes = (uint32_t)RB * p.ld * 4u;
-    float* stages = reinterpret_cast<float*>(smem_raw);
+    const uint32_t row_bytes = (uint32_t)p.ld * EB;
+    const uint32_t stage_bytes = (uint32_t)RB * row_bytes;
+    unsigned char* stages = smem_raw;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)p.n_stages * stage_bytes);
     uint64_t* empty = full + GD_MAX_STAGES;
     float* red = reinterpret_cast<float*>(empty + GD_MAX_STAGES);      // [2][8][RB]
@@ -54,20 +69,20 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
         // producer warp: prefetch the first tiles while the parameters are still in flight
         long long issued = 0;
         uint64_t pol = l2_policy_evict_first();
+        auto issue = [&](long long k) {
+            const long long step = jv.bl + k * (long long)jv.Gj;
+            const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
+            const int row0 = (int)(step % p.steps_per_seg) * RB;
+            const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
+            const uint32_t bytes = (uint32_t)nr * row_bytes;
+            const int st = (int)(k % p.n_stages);
+            mbar_arrive_expect_tx(&full[st], bytes);
+            tma_load_1d(stages + (size_t)st * stage_bytes,
+                        reinterpret_cast<const unsigned char*>(p.seg_X[sg]) + (size_t)row0 * row_bytes, bytes, &full[st], pol);
+        };
         if (lane == 0) {
             const long long pre = my_steps < p.n_stages ? my_steps : p.n_stages;
-            for (; issued < pre; ++issued) {
-                const long long step = jv.bl + issued * (long long)jv.Gj;
-                const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
-                const int row0 = (int)(step % p.steps_per_seg) * RB;
-                const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
-                const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
-                const int st = (int)(issued % p.n_stages);
-                mbar_arrive_expect_tx(&full[st], bytes);
-                tma_load_1d(stages + (size_t)st * RB * p.ld, p.seg_X[sg] + (size_t)row0 * p.ld, bytes, &full[st], pol);
-            }
-        }
-        if (lane == 0) {
+            for (; issued < pre; ++issued) issue(issued);
             code = wait_for_parameters(p);
             s_decision = code;
         }
@@ -86,13 +101,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
                 const int st = (int)(k % p.n_stages);
                 const uint32_t use = (uint32_t)(k / p.n_stages);      // >= 1 here
                 mbar_wait(&empty[st], (use - 1) & 1);
-                const long long step = jv.bl + k * (long long)jv.Gj;
-                const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
-                const int row0 = (int)(step % p.steps_per_seg) * RB;
-                const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
-                const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
-                mbar_arrive_expect_tx(&full[st], bytes);
-                tma_load_1d(stages + (size_t)st * RB * p.ld, p.seg_X[sg] + (size_t)row0 * p.ld, bytes, &full[st], pol);
+                issue(k);
             }
         }
         __syncwarp();
@@ -101,20 +110,17 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
         code = s_decision;
         if (code == DEC_SKIP) return;
 
-        // ---------------- consumers
-        const int ld4 = p.ld >> 2;
-        float4 bt[DV], acc[DV];
+        // ---------------- consumers: thread owns vectors cv = v*256 + tid, i.e. columns cv*E .. cv*E+E-1
+        const int ldv = p.ld / E;
+        float bt[DV][E], acc[DV][E];
 #pragma unroll
         for (int v = 0; v < DV; ++v) {
-            const int c4 = v * GD_CONSUMERS + tid;
-            acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            const int c = c4 * 4;
-            if (c + 0 < p.d) t.x = p.beta[c + 0];
-            if (c + 1 < p.d) t.y = p.beta[c + 1];
-            if (c + 2 < p.d) t.z = p.beta[c + 2];
-            if (c + 3 < p.d) t.w = p.beta[c + 3];
-            bt[v] = t;
+            const int c = (v * GD_CONSUMERS + tid) * E;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                acc[v][e] = 0.f;
+                bt[v][e] = (c + e < p.d) ? p.beta[c + e] : 0.f;
+            }
         }
         for (long long k = 0; k < my_steps; ++k) {
             const int st = (int)(k % p.n_stages);
@@ -130,21 +136,20 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
 #pragma unroll
             for (int r = 0; r < RB; ++r) yv[r] = (r < nr) ? __ldg(ys + r) : 0.f;
             mbar_wait(&full[st], use & 1);
-            const float4* tile = reinterpret_cast<const float4*>(stages + (size_t)st * RB * p.ld);
-            float4 x[RB][DV];
+            const uint4* tile = reinterpret_cast<const uint4*>(stages + (size_t)st * stage_bytes);
+            float x[RB][DV][E];
             float dot[RB];
 #pragma unroll
             for (int r = 0; r < RB; ++r) {
                 dot[r] = 0.f;
 #pragma unroll
                 for (int v = 0; v < DV; ++v) {
-                    const int c4 = v * GD_CONSUMERS + tid;
-                    x[r][v] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (r < nr && c4 < ld4) x[r][v] = tile[(size_t)r * ld4 + c4];
-                    dot[r] = fmaf(x[r][v].x, bt[v].x, dot[r]);
-                    dot[r] = fmaf(x[r][v].y, bt[v].y, dot[r]);
-                    dot[r] = fmaf(x[r][v].z, bt[v].z, dot[r]);
-                    dot[r] = fmaf(x[r][v].w, bt[v].w, dot[r]);
+                    const int cv = v * GD_CONSUMERS + tid;
+                    uint4 q = make_uint4(0u, 0u, 0u, 0u);
+                    if (r < nr && cv < ldv) q = tile[(size_t)r * ldv + cv];
+                    unpack16<E>(q, x[r][v]);
+#pragma unroll
+                    for (int e = 0; e < E; ++e) dot[r] = fmaf(x[r][v][e], bt[v][e], dot[r]);
                 }
             }
 #pragma unroll
@@ -166,21 +171,23 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
                     for (int w = 0; w < GD_CONSUMER_WARPS; ++w) pr += redk[w * RB + r];
                     const float rs = cf * residual(p.model, pr, yv[r]);
 #pragma unroll
-                    for (int v = 0; v < DV; ++v) {
-                        acc[v].x = fmaf(rs, x[r][v].x, acc[v].x);
-                        acc[v].y = fmaf(rs, x[r][v].y, acc[v].y);
-                        acc[v].z = fmaf(rs, x[r][v].z, acc[v].z);
-                        acc[v].w = fmaf(rs, x[r][v].w, acc[v].w);
-                    }
+                    for (int v = 0; v < DV; ++v)
+#pragma unroll
+                        for (int e = 0; e < E; ++e) acc[v][e] = fmaf(rs, x[r][v][e], acc[v][e]);
                 }
             }
         }
-        // ---------------- per-CTA partial -> scratch
-        float4* mine = reinterpret_cast<float4*>(p.partials + (size_t)b * p.ldp);
+        // ---------------- per-CTA partial -> scratch (fp32)
+        float4* mine = reinterpret_cast<float4*>(p.partials + (size_t)blockIdx.x * p.ldp);
 #pragma unroll
         for (int v = 0; v < DV; ++v) {
-            const int c4 = v * GD_CONSUMERS + tid;
-            if (c4 < ld4) __stcg(mine + c4, acc[v]);
+            const int cv = v * GD_CONSUMERS + tid;
+            if (cv < ldv) {
+#pragma unroll
+                for (int h = 0; h < E / 4; ++h)
+                    __stcg(mine + (size_t)cv * (E / 4) + h,
+                           make_float4(acc[v][4 * h], acc[v][4 * h + 1], acc[v][4 * h + 2], acc[v][4 * h + 3]));
+            }
         }
     }
 
@@ -215,10 +222,10 @@ int assign_ctas(GradParams& p, int sm_count) {
     return used;
 }
 
-template <int DV, int RB>
+template <int E, int DV, int RB>
 static int launch(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
     const DevInfo& di = dev_info();
-    const size_t stage_bytes = (size_t)RB * p.ld * 4;
+    const size_t stage_bytes = (size_t)RB * p.ld * (16 / E);
     int stages = (int)((GD_SMEM_BUDGET - 1024) / stage_bytes);
     if (stages > GD_MAX_STAGES) stages = GD_MAX_STAGES;
     EH_REQUIRE(stages >= 2, "grad_dense: row tile too large for shared memory (ld=%d)", p.ld);
@@ -227,7 +234,7 @@ static int launch(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStre
     if (smem < 8 * 32 * sizeof(float4) + tail) smem = 8 * 32 * sizeof(float4) + tail;
     p.n_stages = stages;
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
-    auto kern = grad_dense_kernel<DV, RB>;
+    auto kern = grad_dense_kernel<E, DV, RB>;
     static bool attr_done = false;
     if (!attr_done) {
         EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
@@ -250,8 +257,11 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
     EH_REQUIRE(j0->d_beta, "grad_dense: null parameters");
     EH_REQUIRE(j0->rows_per_seg > 0 && j0->d > 0, "grad_dense: empty problem");
     EH_REQUIRE(j0->ld >= j0->d && (j0->ld % 4) == 0, "grad_dense: ld (%d) must be >= d and a multiple of 4", j0->ld);
+    EH_REQUIRE(!j0->x_bf16 || ((j0->ld % 8) == 0 && j0->ld <= 16384),
+               "grad_dense: bf16 rows need ld %% 8 == 0 and ld <= 16384 (ld=%d)", j0->ld);
     GradParams p;
     memset(&p, 0, sizeof(p));
+    p.x_bf16 = j0->x_bf16 ? 1 : 0;
     int nseg = 0;
     for (int q = 0; q < n_jobs; ++q) {
         const eh_grad_job* j = &jobs[q];
@@ -259,7 +269,8 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
         EH_REQUIRE(j->n_segs > 0 && j->n_segs <= EH_MAX_SEGS, "grad_dense: n_segs=%d out of range (1..%d)", j->n_segs,
                    EH_MAX_SEGS);
         EH_REQUIRE(j->d == j0->d && j->ld == j0->ld && j->rows_per_seg == j0->rows_per_seg && j->model == j0->model &&
-                       j->d_beta == j0->d_beta && j->d_beta_flag == j0->d_beta_flag && j->stamp == j0->stamp,
+                       j->d_beta == j0->d_beta && j->d_beta_flag == j0->d_beta_flag && j->stamp == j0->stamp &&
+                       (j->x_bf16 != 0) == (j0->x_bf16 != 0),
                    "grad_dense: batched messages must share shape, model, parameters and stamp");
         EH_REQUIRE(nseg + j->n_segs <= GD_TOTAL_SEGS, "grad_dense: more than %d partitions in one batch", GD_TOTAL_SEGS);
         p.job_seg0[q] = nseg;
@@ -281,7 +292,7 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
     p.stamp = j0->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j0->timeout_ns ? j0->timeout_ns : 30ull * 1000000000ull;
     cudaStream_t st = (cudaStream_t)stream;
-    if (p.ld > 8192) {
+    if (p.ld > 8192 && !p.x_bf16) {
         // two-pass fallback handles one message at a time
         for (int q = 0; q < n_jobs; ++q) {
             GradParams w = p;
@@ -296,10 +307,17 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
         }
         return EH_OK;
     }
+    if (p.x_bf16) {
+        // bf16 rows: 8 columns per 16-byte vector, 256 vectors per row pass
+        if (p.ld <= 2048) return launch<8, 1, 8>(p, d_scratch, scratch_bytes, st);
+        if (p.ld <= 4096) return launch<8, 2, 4>(p, d_scratch, scratch_bytes, st);
+        if (p.ld <= 8192) return launch<8, 4, 2>(p, d_scratch, scratch_bytes, st);
+        return launch<8, 8, 1>(p, d_scratch, scratch_bytes, st);
+    }
     if (p.ld <= 1024) return launch_rowwarp(p, d_scratch, scratch_bytes, st);
-    if (p.ld <= 2048) return launch<2, 8>(p, d_scratch, scratch_bytes, st);
-    if (p.ld <= 4096) return launch<4, 4>(p, d_scratch, scratch_bytes, st);
-    return launch<8, 2>(p, d_scratch, scratch_bytes, st);
+    if (p.ld <= 2048) return launch<4, 2, 8>(p, d_scratch, scratch_bytes, st);
+    if (p.ld <= 4096) return launch<4, 4, 4>(p, d_scratch, scratch_bytes, st);
+    return launch<4, 8, 2>(p, d_scratch, scratch_bytes, st);
 }
 
 }  // namespace eh

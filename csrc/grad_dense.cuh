@@ -23,7 +23,7 @@ struct GradScratchHdr {          // first 512 bytes of the scratch buffer
 constexpr uint32_t DEC_GO = 1, DEC_SKIP = 2;
 
 struct GradParams {
-    const float* seg_X[GD_TOTAL_SEGS];
+    const void* seg_X[GD_TOTAL_SEGS];   // fp32 rows, or bf16 rows when x_bf16
     const float* seg_y[GD_TOTAL_SEGS];
     const float* beta;
     float* out;                      // single-message paths (wide fallback)
@@ -36,6 +36,7 @@ struct GradParams {
     int job_seg0[GD_MAX_JOBS];
     int job_nsegs[GD_MAX_JOBS];
     int n_jobs;
+    int x_bf16;
     const uint32_t* beta_flag;
     uint32_t* err;
     GradScratchHdr* hdr;

@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
             const int st = (int)(k % p.n_stages);
             mbar_arrive_expect_tx(&full[st], bytes);
-            tma_load_1d(stages + (size_t)st * RB * p.ld, p.seg_X[sg] + (size_t)row0 * p.ld, bytes, &full[st], pol);
+            tma_load_1d(stages + (size_t)st * RB * p.ld, reinterpret_cast<const float*>(p.seg_X[sg]) + (size_t)row0 * p.ld, bytes,
+                        &full[st], pol);
         };
         if (lane == 0) {
             const long long pre = my_steps < p.n_stages ? my_steps : p.n_stages;

@@ -95,7 +95,7 @@ int launch_wide(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream
     for (int sg = 0; sg < p.n_segs; ++sg) {
         for (int r0 = 0; r0 < p.rows_per_seg; r0 += WIDE_CHUNK) {
             const int rows = (p.rows_per_seg - r0) < WIDE_CHUNK ? (p.rows_per_seg - r0) : WIDE_CHUNK;
-            const float* X = p.seg_X[sg] + (size_t)r0 * p.ld;
+            const float* X = reinterpret_cast<const float*>(p.seg_X[sg]) + (size_t)r0 * p.ld;
             int blocks = (rows + 7) / 8;
             if (blocks > sm * 8) blocks = sm * 8;
             wide_residual_kernel<<<blocks, 256, 0, st>>>(X, p.seg_y[sg] + r0, p.beta, rows, p.d, p.ld, p.coeff[sg],

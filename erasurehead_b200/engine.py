@@ -113,6 +113,9 @@ class Engine:
         mine = ctx.local_workers(spec.n)
         needed = sorted({sg.partition for w in mine for sg in spec.segments[w]})
         self.sparse = bool(self.data.is_sparse) if self.data is not None else False
+        self.bf16 = cfg.dtype == "bf16" and not self.sparse and not self.mc
+        if cfg.dtype not in ("fp32", "bf16"):
+            raise ValueError("dtype must be fp32 or bf16")
         for p in needed:
             self.parts[p] = self._device_partition(p)
         # ---- worker jobs (private message first: it is sent first, partial_coded.py:229,234)
@@ -128,7 +131,8 @@ class Engine:
                             f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
                             "use fewer partitions per worker")
                 j = _lib.WorkerJob()
-                j.worker, j.msg, j.sparse, j.model = w, kind, (2 if self.mc else int(self.sparse)), self.model.device_id
+                jkind = 2 if self.mc else (1 if self.sparse else (3 if self.bf16 else 0))
+                j.worker, j.msg, j.sparse, j.model = w, kind, jkind, self.model.device_id
                 j.classes = self.model.n_out
                 j.n_segs, j.rows_per_seg, j.d = len(segs), spec.rows_per_part, d
                 X0 = self.parts[segs[0].partition][0]
@@ -163,7 +167,13 @@ class Engine:
         self.plan = plan
 
     def _device_partition(self, p: int):
-        """(X or ELL idx, y) of partition ``p`` on this GPU, float32 / int32."""
+        """(X or ELL idx, y) of partition ``p`` on this GPU (fp32, bf16 when ``--dtype=bf16``, int32 ELL)."""
+        X, y = self._device_partition_fp32(p)
+        if getattr(self, "bf16", False):
+            X = X.to(self.torch.bfloat16)
+        return X, y
+
+    def _device_partition_fp32(self, p: int):
         torch = self.torch
         dev = self.ctx.device
         cfg, spec = self.cfg, self.spec
@@ -450,6 +460,8 @@ class Engine:
         use_tc = (not self.sparse) and cfg.eval_precision == "tf32"
         for p in range(n_parts):
             Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
+            if Xp.dtype == torch.bfloat16:
+                Xp = Xp.float()                     # evaluation kernels take fp32 rows (exact widening)
             if use_tc:
                 mops.eval_tc(Xp, Bt, yp, kind=kind, d=d, loss_sums=tr)
             else:

@@ -54,7 +54,7 @@ def make_dense_job(Xs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], beta_
     """One message = the listed partitions (equal row counts, same row stride)."""
     X0 = Xs[0]
     for X, y in zip(Xs, ys):
-        assert X.dtype == torch.float32 and X.dim() == 2 and X.stride(1) == 1
+        assert X.dtype in (torch.float32, torch.bfloat16) and X.dtype == X0.dtype and X.dim() == 2 and X.stride(1) == 1
         assert X.shape[0] == X0.shape[0] and X.stride(0) == X0.stride(0)
         assert y.dtype == torch.float32 and y.is_contiguous() and y.numel() == X.shape[0]
     job = GradJob()
@@ -63,6 +63,7 @@ def make_dense_job(Xs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], beta_
     job.d_flag, job.d_beta_flag, job.d_err = flag_ptr, beta_flag_ptr, err_ptr
     job.rows_per_seg, job.d, job.ld = X0.shape[0], int(d), X0.stride(0)
     job.model, job.stamp, job.timeout_ns = int(model), int(stamp), int(timeout_ns)
+    job.x_bf16 = int(X0.dtype == torch.bfloat16)
     return job
 
 

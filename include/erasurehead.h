@@ -85,7 +85,7 @@ int eh_ws_error(const eh_ws_layout* lay, void* d_ws, int* err, void* stream);
 #define EH_MAX_SEGS 16
 
 typedef struct eh_grad_job {
-    const float*    d_X[EH_MAX_SEGS];   /* per segment: [rows_per_seg, ld] row-major fp32, 16B aligned */
+    const void*     d_X[EH_MAX_SEGS];   /* per segment: [rows_per_seg, ld] row-major fp32 (or bf16), 16B aligned */
     const float*    d_y[EH_MAX_SEGS];   /* per segment: [rows_per_seg] labels / targets */
     float           coeff[EH_MAX_SEGS]; /* per segment encode weight (B[w, partition] or 1) */
     const float*    d_beta;         /* [d] parameters (buffer of this round) */
@@ -99,6 +99,8 @@ typedef struct eh_grad_job {
     int32_t         model;
     uint32_t        stamp;          /* round + 1 */
     uint64_t        timeout_ns;     /* watchdog for the beta wait (0 = 30 s) */
+    int32_t         x_bf16;         /* 0: d_X are fp32 rows; 1: bf16 rows (ld in elements, ld % 8 == 0) */
+    int32_t         reserved;
 } eh_grad_job;
 
 size_t eh_grad_dense_scratch_bytes(int d);
@@ -225,7 +227,7 @@ int eh_decoder_publish(const eh_decoder_desc* desc, int round, void* stream);
 typedef struct eh_worker_job {
     int32_t  worker;                 /* global worker id (slot row on the root) */
     int32_t  msg;                    /* EH_MSG_CODED / EH_MSG_PRIVATE */
-    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL, 2: dense multi-column (tensor cores) */
+    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL, 2: dense multi-column (tensor cores), 3: dense bf16 rows */
     int32_t  model;
     int32_t  n_segs, rows_per_seg;
     int32_t  d, ld_or_nnz;           /* dense: row stride; ELL: ones per row */

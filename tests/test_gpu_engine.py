@@ -227,3 +227,19 @@ def test_random_scheme_configurations_match_oracle():
         assert np.abs(res.betaset - ref.betaset).max() <= tol, (scheme, n, s, k, P)
         assert np.array_equal(res.n_collected, ref.n_collected), (scheme, n, s, k, P)
         eng.close()
+
+
+def test_engine_bf16_storage_matches_oracle_on_rounded_data():
+    cfg = mk("approx", s=1, k=5, d=1200, rows=8 * 300, dtype="bf16")
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1)
+    # the oracle sees the same bf16-rounded features
+    data.parts = [torch.from_numpy(p).to(torch.bfloat16).double().numpy() for p in data.parts]
+    dl = spaced_delays(cfg.rounds, 8, seed=5)
+    eng = Engine(cfg, data, delays=dl)
+    assert eng.bf16 and eng.parts[0][0].dtype == torch.bfloat16
+    res = eng.run()
+    ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl, beta0=eng.beta0)
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-4 * max(1.0, np.abs(ref.betaset).max())
+    ev = eng.evaluate(res)
+    assert np.all(np.isfinite(ev.training_loss))
+    eng.close()

@@ -229,3 +229,19 @@ def test_grad_dense_multi_batches_messages_in_one_launch(d):
     single = grad.grad_dense([parts[1][0], parts[2][0], parts[3][0]], [parts[1][1], parts[2][1], parts[3][1]], beta,
                              coeff=[0.5, -2.0, 1.5], d=d, scratch=sc)
     assert torch.allclose(single, outs[1], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("rows,d", [(200, 64), (1000, 1500), (777, 4096), (300, 8000)])
+@pytest.mark.parametrize("model", [0, 1])
+def test_grad_dense_bf16_rows(rows, d, model):
+    """bf16 feature storage (half the HBM traffic): exact against the reference on the same bf16 values."""
+    from erasurehead_b200.ops import grad, synth
+    torch.manual_seed(rows + d)
+    ld = synth.pad_cols(d)
+    Xb = torch.zeros(rows, ld, device=DEV, dtype=torch.bfloat16)
+    Xb[:, :d] = (torch.randn(rows, d, device=DEV) / np.sqrt(d)).to(torch.bfloat16)
+    y = torch.where(torch.rand(rows, device=DEV) > 0.5, 1.0, -1.0) if model == 0 else torch.randn(rows, device=DEV)
+    beta = torch.randn(d, device=DEV)
+    g = grad.grad_dense([Xb, Xb], [y, y], beta, coeff=(1.25, -0.5), model=model, d=d)
+    want = ref_grad(Xb[:, :d].float(), y, beta, 0.75, model)
+    assert (g.double() - want).abs().max().item() <= 2e-4 * max(1.0, want.abs().max().item())
