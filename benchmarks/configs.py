@@ -179,6 +179,18 @@ def bench_multi(ctx, a):
         eng.close()
 
 
+def bench_latency(ctx, a):
+    """Protocol cost of one round: tiny data, no injected delay (launch + flags + NVLink ship + decode + push)."""
+    for scheme, s, k in (("approx", 1, 4), ("coded", 2, 0), ("naive", 0, 0)):
+        cfg = mkcfg(scheme, 8, s, 8 * 256, 4096, k=k, rounds=260, synthetic=True, seed=1, add_delay=0)
+        eng = Engine(cfg, None, ctx=ctx)
+        ms = timed_rounds(ctx, eng, 20, 200)
+        emit(ctx, {"config": "round_latency", "scheme": scheme, "gpus": ctx.world, "n_workers": 8, "d": 4096,
+                   "rows_per_partition": 256, "us_per_round": ms * 1e3, "message_bytes": 4096 * 4,
+                   "kernels_per_round_rank0": eng.launches_per_round()})
+        eng.close()
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="exact,sweep,amazon,multi")
@@ -199,6 +211,8 @@ if __name__ == "__main__":
         bench_amazon(ctx, a)
     if "multi" in which:
         bench_multi(ctx, a)
+    if "latency" in which:
+        bench_latency(ctx, a)
     if a.out and ctx.is_root:
         json.dump(OUT, open(a.out, "w"), indent=1)
     if ctx.world > 1:

@@ -245,3 +245,13 @@ def test_grad_dense_bf16_rows(rows, d, model):
     g = grad.grad_dense([Xb, Xb], [y, y], beta, coeff=(1.25, -0.5), model=model, d=d)
     want = ref_grad(Xb[:, :d].float(), y, beta, 0.75, model)
     assert (g.double() - want).abs().max().item() <= 2e-4 * max(1.0, want.abs().max().item())
+
+
+def test_predict_margins_on_gpu_uses_tensor_core_path():
+    from erasurehead_b200 import predict
+    torch.manual_seed(0)
+    X = torch.randn(500, 70, device=DEV)
+    B = torch.randn(6, 70, device=DEV) * 0.1
+    P = predict.margins(X, B)
+    assert (P.double() - X.double() @ B.double().t()).abs().max().item() < 5e-3
+    assert predict.predict_proba(X, B[0]).shape == (500,)

@@ -128,3 +128,13 @@ def test_metrics_jsonl_and_npy_outputs(tmp_path):
     rd = out["results_dir"]
     for suffix in ("betaset", "timeset", "worker_timeset", "training_loss", "testing_loss", "auc"):
         assert os.path.exists(f"{rd}approx_acc_1_5_{suffix}.npy")
+
+
+def test_predict_helpers_host():
+    from erasurehead_b200 import predict
+    rng = np.random.RandomState(0)
+    X, B = rng.randn(20, 5), rng.randn(3, 5)
+    assert np.allclose(predict.margins(X, B), X @ B.T)
+    assert np.allclose(predict.predict_proba(X, B[0]), 1 / (1 + np.exp(-X @ B[0])))
+    assert set(np.unique(predict.predict_label(X, B[0]))) <= {-1.0, 1.0}
+    assert predict.predict_class(X, rng.randn(5, 4)).shape == (20,)
