@@ -19,6 +19,8 @@
 //
 // The kernel starts prefetching X while it still waits for this round's parameters
 // (`d_beta_flag`), i.e. the parameter broadcast overlaps the first tiles of the next round.
+#include <stdlib.h>
+
 #include "grad_dense.cuh"
 
 namespace eh {
@@ -314,7 +316,8 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
         if (p.ld <= 8192) return launch<8, 4, 2>(p, d_scratch, scratch_bytes, st);
         return launch<8, 8, 1>(p, d_scratch, scratch_bytes, st);
     }
-    if (p.ld <= 1024) return launch_rowwarp(p, d_scratch, scratch_bytes, st);
+    if (p.ld <= 1024 || (p.ld <= 2048 && getenv("EH_ROWBLOCK_2048") == nullptr))
+        return launch_rowwarp(p, d_scratch, scratch_bytes, st);
     if (p.ld <= 2048) return launch<4, 2, 8>(p, d_scratch, scratch_bytes, st);
     if (p.ld <= 4096) return launch<4, 4, 4>(p, d_scratch, scratch_bytes, st);
     return launch<4, 8, 2>(p, d_scratch, scratch_bytes, st);

@@ -97,7 +97,10 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             if (c + 3 < p.d) t.w = p.beta[c + 3];
             bt[v] = t;
         }
-        const int rows_per_pass = GD_CONSUMER_WARPS * RPW;       // rows the CTA covers per pass
+        // U rows in flight per lane group: narrow rows are latency-bound (shuffle + exp chain per row)
+        constexpr int U = (DVW <= 2) ? 4 : (DVW <= 8 ? 2 : 1);
+        const int rows_per_group = GD_CONSUMER_WARPS * RPW;      // rows the CTA covers per sub-pass
+        const int rows_per_pass = rows_per_group * U;
         for (long long k = 0; k < my_steps; ++k) {
             const int st = (int)(k % p.n_stages);
             const uint32_t use = (uint32_t)(k / p.n_stages);
@@ -110,30 +113,41 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             mbar_wait(&full[st], use & 1);
             const float4* tile = reinterpret_cast<const float4*>(stages + (size_t)st * RB * p.ld);
             for (int r0 = 0; r0 < nr; r0 += rows_per_pass) {
-                const int r = r0 + warp * RPW + sub;
-                const bool valid = r < nr;
-                float4 x[DVW];
-                float dot = 0.f;
-                const float yv = valid ? __ldg(ys + r) : 0.f;
+                float4 x[U][DVW];
+                float dot[U], yv[U];
+                bool valid[U];
 #pragma unroll
-                for (int v = 0; v < DVW; ++v) {
-                    const int c4 = v * LPR + pos;
-                    x[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (valid && c4 < ld4) x[v] = tile[(size_t)r * ld4 + c4];
-                    dot = fmaf(x[v].x, bt[v].x, dot);
-                    dot = fmaf(x[v].y, bt[v].y, dot);
-                    dot = fmaf(x[v].z, bt[v].z, dot);
-                    dot = fmaf(x[v].w, bt[v].w, dot);
+                for (int u = 0; u < U; ++u) {
+                    const int r = r0 + u * rows_per_group + warp * RPW + sub;
+                    valid[u] = r < nr;
+                    yv[u] = valid[u] ? __ldg(ys + r) : 0.f;
+                    dot[u] = 0.f;
+#pragma unroll
+                    for (int v = 0; v < DVW; ++v) {
+                        const int c4 = v * LPR + pos;
+                        x[u][v] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid[u] && c4 < ld4) x[u][v] = tile[(size_t)r * ld4 + c4];
+                        dot[u] = fmaf(x[u][v].x, bt[v].x, dot[u]);
+                        dot[u] = fmaf(x[u][v].y, bt[v].y, dot[u]);
+                        dot[u] = fmaf(x[u][v].z, bt[v].z, dot[u]);
+                        dot[u] = fmaf(x[u][v].w, bt[v].w, dot[u]);
+                    }
                 }
 #pragma unroll
-                for (int o = LPR / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-                const float rs = valid ? cf * residual(p.model, dot, yv) : 0.f;
+                for (int o = LPR / 2; o > 0; o >>= 1) {
 #pragma unroll
-                for (int v = 0; v < DVW; ++v) {
-                    acc[v].x = fmaf(rs, x[v].x, acc[v].x);
-                    acc[v].y = fmaf(rs, x[v].y, acc[v].y);
-                    acc[v].z = fmaf(rs, x[v].z, acc[v].z);
-                    acc[v].w = fmaf(rs, x[v].w, acc[v].w);
+                    for (int u = 0; u < U; ++u) dot[u] += __shfl_xor_sync(0xffffffffu, dot[u], o);
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const float rs = valid[u] ? cf * residual(p.model, dot[u], yv[u]) : 0.f;
+#pragma unroll
+                    for (int v = 0; v < DVW; ++v) {
+                        acc[v].x = fmaf(rs, x[u][v].x, acc[v].x);
+                        acc[v].y = fmaf(rs, x[u][v].y, acc[v].y);
+                        acc[v].z = fmaf(rs, x[u][v].z, acc[v].z);
+                        acc[v].w = fmaf(rs, x[u][v].w, acc[v].w);
+                    }
                 }
             }
             __syncwarp();
@@ -182,7 +196,8 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
     const int row_bytes = p.ld * 4;
     // rows per stage: ~32 KB, a multiple of the rows the CTA covers per pass
     int RB = (32 * 1024) / row_bytes;
-    const int pass = GD_CONSUMER_WARPS * RPW;
+    constexpr int U = (DVW <= 2) ? 4 : (DVW <= 8 ? 2 : 1);
+    const int pass = GD_CONSUMER_WARPS * RPW * U;
     if (RB < pass) RB = pass;
     RB = RB / pass * pass;
     if (RB > p.rows_per_seg) RB = (p.rows_per_seg + pass - 1) / pass * pass;
@@ -221,7 +236,8 @@ int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStr
     if (p.ld <= 128) return launch_rw<32, 1>(p, d_scratch, scratch_bytes, stream);
     if (p.ld <= 256) return launch_rw<32, 2>(p, d_scratch, scratch_bytes, stream);
     if (p.ld <= 512) return launch_rw<32, 4>(p, d_scratch, scratch_bytes, stream);
-    return launch_rw<32, 8>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 1024) return launch_rw<32, 8>(p, d_scratch, scratch_bytes, stream);
+    return launch_rw<32, 16>(p, d_scratch, scratch_bytes, stream);
 }
 
 }  // namespace eh
