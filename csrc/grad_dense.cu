@@ -304,7 +304,12 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
                 w.coeff[i] = p.coeff[p.job_seg0[q] + i];
             }
             w.n_segs = p.job_nsegs[q]; w.out = p.job_out[q]; w.flag = p.job_flag[q];
-            int rc = launch_wide(w, d_scratch, scratch_bytes, st);
+            w.seq = next_launch_seq();
+            // one pass on thread-block clusters when the row can be split over 4 or 8 CTAs,
+            // else (or with EH_WIDE=twopass) the two-pass fallback
+            const bool cluster_ok = p.ld <= 32768 && (p.ld % 32) == 0 && getenv("EH_WIDE_TWOPASS") == nullptr;
+            int rc = cluster_ok ? launch_cluster(w, d_scratch, scratch_bytes, st)
+                                : launch_wide(w, d_scratch, scratch_bytes, st);
             if (rc) return rc;
         }
         return EH_OK;

@@ -173,5 +173,6 @@ __device__ __forceinline__ uint32_t wait_for_parameters(const GradParams& p) {
 int assign_ctas(GradParams& p, int sm_count);
 int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
 int launch_wide(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
+int launch_cluster(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream);
 
 }  // namespace eh

@@ -21,7 +21,7 @@ def ref_grad(X, y, beta, coeff, model):
 
 
 @pytest.mark.parametrize("rows,d", [(64, 16), (1000, 100), (517, 1024), (300, 1500), (1024, 4096), (96, 8000),
-                                    (700, 20000)])
+                                    (700, 20000), (500, 12288), (333, 32768), (150, 40000)])
 @pytest.mark.parametrize("model", [0, 1])
 def test_grad_dense_matches_reference(rows, d, model):
     from erasurehead_b200.ops import grad, synth
