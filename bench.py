@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--scheme", default="approx")
     ap.add_argument("--delay-scale", type=float, default=DELAY_SCALE)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--beta-push", default="p2p", choices=["p2p", "multicast"])
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"], help="feature storage (headline: fp32)")
     return ap.parse_args()
 
@@ -125,7 +126,7 @@ def main():
     ic, pp, cv = triple_from_scheme(args.scheme)
     n_rows = n * args.rows
     cfg = RunConfig(n + 1, n_rows, args.cols, "", 0, "x", ic, s, pp, cv, k, 1, "AGD", rounds=2 * (W + K) + 2,
-                    synthetic=True, seed=1, delay_scale=args.delay_scale, quiet=True, dtype=args.dtype)
+                    synthetic=True, seed=1, delay_scale=args.delay_scale, quiet=True, dtype=args.dtype, beta_push=args.beta_push)
     if args.impl == "nccl":
         from erasurehead_b200.parallel.nccl_baseline import NcclBaselineEngine as Eng
     else:

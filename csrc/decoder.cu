@@ -270,8 +270,12 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
                 }
             }
             const float4 out = make_float4(bn[0], bn[1], bn[2], bn[3]);
-            for (int pe = 0; pe < D.n_peers; ++pe)
-                *(reinterpret_cast<float4*>(ws_beta(D.d_ws_peer[pe], D.lay, nxt)) + c4) = out;
+            if (D.d_beta_mc) {
+                multimem_st_v4(D.d_beta_mc + (size_t)nxt * D.d_pad + (size_t)c4 * 4, out);      // NVLS: fan-out in the switch
+            } else {
+                for (int pe = 0; pe < D.n_peers; ++pe)
+                    *(reinterpret_cast<float4*>(ws_beta(D.d_ws_peer[pe], D.lay, nxt)) + c4) = out;
+            }
         }
     }
     // ------------------------------------------------------------------ phase 3: publish
@@ -306,8 +310,12 @@ __global__ void publish_push_kernel(const eh_decoder_desc D, const int round) {
             v[e] = (c < D.d) ? (float)D.d_beta64[c] : 0.f;
         }
         const float4 out = make_float4(v[0], v[1], v[2], v[3]);
-        for (int pe = 0; pe < D.n_peers; ++pe)
-            *(reinterpret_cast<float4*>(ws_beta(D.d_ws_peer[pe], D.lay, par)) + c4) = out;
+        if (D.d_beta_mc) {
+            multimem_st_v4(D.d_beta_mc + (size_t)par * D.d_pad + (size_t)c4 * 4, out);
+        } else {
+            for (int pe = 0; pe < D.n_peers; ++pe)
+                *(reinterpret_cast<float4*>(ws_beta(D.d_ws_peer[pe], D.lay, par)) + c4) = out;
+        }
     }
     __threadfence_system();
 }

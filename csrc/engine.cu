@@ -35,7 +35,8 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                        "run_rounds: job %d addresses slot (%d,%d) outside the workspace", q, wj.worker, wj.msg);
             float* out = ws_slot(plan->d_ws_root, lay, wj.worker, wj.msg, par);
             uint32_t* flag = ws_flag(plan->d_ws_root, lay, wj.worker, wj.msg);
-            const float* beta = ws_beta(plan->d_ws_local, lay, par);
+            const float* beta = plan->d_beta_local ? plan->d_beta_local + (size_t)par * lay.d_pad
+                                                   : ws_beta(plan->d_ws_local, lay, par);
             int rc = EH_OK;
             if (wj.sparse == 2) {
                 rc = flush();

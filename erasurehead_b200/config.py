@@ -102,6 +102,7 @@ class RunConfig:
     metrics_jsonl: Optional[str] = None
     decode: str = "auto"                   # auto | table | solve
     quiet: bool = False
+    beta_push: str = "p2p"                 # parameter broadcast: p2p (peer stores) | multicast (NVLS multimem.st)
     dtype: str = "fp32"                    # storage of dense features on the GPU: fp32 | bf16 (half the HBM traffic)
     debug_poison: bool = False             # fill every message slot with NaN before a run (stale-read detector)
 

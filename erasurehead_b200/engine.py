@@ -152,6 +152,21 @@ class Engine:
             sb = max(sb, L.eh_grad_mc_scratch_bytes(int(spec.rows_per_part), int(d), int(self.model.n_out)))
         self.scratch = gops.Scratch(sb, dev)
         self.timeout_ns = int(120e9)
+        # ---- optional NVLS multicast parameter buffer (torch symmetric memory provides the mapping)
+        self.beta_mc_ptr = self.beta_local_ptr = 0
+        if cfg.beta_push == "multicast" and ctx.world > 1:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            self._symm_beta = symm.empty(2 * int(lay.d_pad), dtype=torch.float32, device=dev)
+            self._symm_handle = symm.rendezvous(self._symm_beta, dist.group.WORLD.group_name)
+            mc = getattr(self._symm_handle, "multicast_ptr", 0)
+            if not mc:
+                raise RuntimeError("--beta-push=multicast: this system exposes no NVLS multicast mapping")
+            self.beta_mc_ptr = int(mc)
+            self.beta_local_ptr = int(self._symm_handle.buffer_ptrs[ctx.rank])
+            self._symm_beta.zero_()
+        elif cfg.beta_push not in ("p2p", "multicast"):
+            raise ValueError("beta_push must be p2p or multicast")
         # ---- decoder state (root)
         self.dec = None
         if ctx.is_root:
@@ -161,6 +176,7 @@ class Engine:
         plan.jobs = C.cast(self._jobs, C.POINTER(_lib.WorkerJob))
         plan.d_ws_local, plan.d_ws_root = self.ws.local, self.ws.root
         plan.d_scratch, plan.scratch_bytes = self.scratch.ptr(), self.scratch.nbytes
+        plan.d_beta_local = self.beta_local_ptr or None
         plan.decoder = C.pointer(self.dec) if self.dec is not None else None
         plan.timeout_ns = self.timeout_ns
         plan.lay = lay
@@ -244,6 +260,7 @@ class Engine:
         D.d_worker_timeset, D.d_weights = self.t_wts.data_ptr(), self.t_weights.data_ptr()
         D.d_ncollected, D.d_tstart = self.t_ncol.data_ptr(), self.t_tstart.data_ptr()
         D.d_scratch = self.t_decscratch.data_ptr()
+        D.d_beta_mc = self.beta_mc_ptr or None
         D.alpha, D.n_rows, D.lr_scale = float(cfg.alpha), float(cfg.n_rows), float(spec.lr_scale)
         D.timeout_ns = self.timeout_ns
         D.lay = self.ws.lay

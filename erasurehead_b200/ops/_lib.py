@@ -86,7 +86,7 @@ class DecoderDesc(C.Structure):
                 ("d_ws_local", C.c_void_p), ("d_ws_peer", C.c_void_p * EH_MAX_PEERS),
                 ("d_betaset", C.c_void_p), ("d_timeset", C.c_void_p), ("d_worker_timeset", C.c_void_p),
                 ("d_weights", C.c_void_p), ("d_ncollected", C.c_void_p), ("d_tstart", C.c_void_p),
-                ("d_scratch", C.c_void_p),
+                ("d_scratch", C.c_void_p), ("d_beta_mc", C.c_void_p),
                 ("alpha", C.c_double), ("n_rows", C.c_double), ("lr_scale", C.c_double),
                 ("timeout_ns", C.c_uint64), ("lay", WsLayout)]
 
@@ -94,7 +94,7 @@ class DecoderDesc(C.Structure):
 class RoundPlan(C.Structure):
     _fields_ = [("n_jobs", C.c_int32), ("reserved", C.c_int32), ("jobs", C.POINTER(WorkerJob)),
                 ("d_ws_local", C.c_void_p), ("d_ws_root", C.c_void_p), ("d_scratch", C.c_void_p),
-                ("scratch_bytes", C.c_size_t), ("decoder", C.POINTER(DecoderDesc)),
+                ("d_beta_local", C.c_void_p), ("scratch_bytes", C.c_size_t), ("decoder", C.POINTER(DecoderDesc)),
                 ("timeout_ns", C.c_uint64), ("lay", WsLayout)]
 
 

@@ -206,6 +206,9 @@ typedef struct eh_decoder_desc {
     int32_t* d_ncollected;          /* [rounds] */
     uint64_t* d_tstart;             /* [1] round-start timestamp carried between launches */
     void*    d_scratch;             /* >= eh_decoder_scratch_bytes() */
+    float*   d_beta_mc;             /* optional NVLS multicast address of a [2][d_pad] parameter buffer that is
+                                       mapped on every GPU: the push becomes ONE multimem.st per 16 bytes instead
+                                       of n_peers stores (NULL = peer stores into each workspace) */
     double   alpha, n_rows, lr_scale;
     uint64_t timeout_ns;            /* watchdog for one round (0 = 60 s) */
     eh_ws_layout lay;
@@ -243,6 +246,8 @@ typedef struct eh_round_plan {
     void*    d_ws_local;             /* this GPU's workspace (parameters + parameter flag) */
     void*    d_ws_root;              /* the root's workspace as mapped here (slots + arrival flags) */
     void*    d_scratch;              /* gradient-kernel scratch (max of the per-job needs) */
+    const float* d_beta_local;       /* optional: this GPU's view of the multicast parameter buffer [2][d_pad]
+                                        (workers read parameters here instead of the workspace) */
     size_t   scratch_bytes;
     const eh_decoder_desc* decoder;  /* non-NULL on the root rank only */
     uint64_t timeout_ns;

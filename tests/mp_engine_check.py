@@ -44,7 +44,8 @@ def main():
         rows, d = kw.pop("rows", 1920), kw.pop("d", 48)
         ic, pp, cv = triple_from_scheme(scheme, P)
         cfg = RunConfig(n + 1, rows, d, "", 0, "x", ic, s, pp, cv, k, 1, "AGD", rounds=6,
-                        gpus=(-1 if device == "cpu" else 0), **kw)
+                        gpus=(-1 if device == "cpu" else 0),
+                        beta_push=os.environ.get("EH_TEST_BETA_PUSH", "p2p"), **kw)
         if name == "sparse":
             cfg.is_real = 1
             data = generate_onehot(rows, d, 13, 8, seed=2)

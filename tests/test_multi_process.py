@@ -17,11 +17,11 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _torchrun(nproc, device, schemes, timeout=300):
+def _torchrun(nproc, device, schemes, timeout=300, extra_env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(HERE, "mp_engine_check.py"), device] + schemes
-    env = dict(os.environ, OMP_NUM_THREADS="1")
+    env = dict(os.environ, OMP_NUM_THREADS="1", **(extra_env or {}))
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env)
     return p.returncode, p.stdout + p.stderr
 
@@ -54,3 +54,12 @@ def test_eight_gpu_peer_path_all_schemes():
     rc, out = _torchrun(8, "cuda", ALL)
     assert rc == 0, out[-3000:]
     assert out.count("OK") == len(ALL)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(_gpu_count() < 2, reason="needs >= 2 GPUs")
+def test_two_gpu_multicast_parameter_push():
+    """NVLS path: the decoder pushes parameters with multimem.st into a multicast-mapped buffer."""
+    rc, out = _torchrun(2, "cuda", ["approx", "coded", "partial_coded"], extra_env={"EH_TEST_BETA_PUSH": "multicast"})
+    assert rc == 0, out[-3000:]
+    assert out.count("OK") == 3
