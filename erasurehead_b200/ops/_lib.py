@@ -14,7 +14,7 @@ import threading
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.abspath(os.path.join(HERE, "..", ".."))
-LIB_PATH = os.path.join(HERE, "liberasurehead.so")
+LIB_PATH = os.environ.get("EH_LIB") or os.path.join(HERE, "liberasurehead.so")   # EH_LIB: A/B a different build
 CSRC = os.path.join(ROOT, "csrc")
 
 EH_MAX_WORKERS = 64
