@@ -5,9 +5,9 @@
 // its 4*DVW columns of the row in registers between the forward dot and the rank-1 accumulate;
 // the warps' private accumulators are combined once at the end.
 //
-//   ld <=   32 : LPR =  8, DVW = 1      ld <=  256 : LPR = 32, DVW = 2
-//   ld <=   64 : LPR = 16, DVW = 1      ld <=  512 : LPR = 32, DVW = 4
-//   ld <=  128 : LPR = 32, DVW = 1      ld <= 1024 : LPR = 32, DVW = 8
+//   ld <=  32 / 64 / 128 / 256 : LPR = 8,  DVW = 1 / 2 / 4 / 8   (4 rows per warp instruction)
+//   ld <=  512                 : LPR = 16, DVW = 8
+//   ld <= 1024 / 2048          : LPR = 32, DVW = 8 / 16
 #include "grad_dense.cuh"
 
 namespace eh {
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             bt[v] = t;
         }
         // U rows in flight per lane group: narrow rows are latency-bound (shuffle + exp chain per row)
-        constexpr int U = (DVW <= 2) ? 4 : (DVW <= 8 ? 2 : 1);
+        constexpr int U = (DVW == 1) ? 8 : (DVW == 2) ? 4 : (DVW <= 8 ? 2 : 1);
         const int rows_per_group = GD_CONSUMER_WARPS * RPW;      // rows the CTA covers per sub-pass
         const int rows_per_pass = rows_per_group * U;
         for (long long k = 0; k < my_steps; ++k) {
@@ -196,7 +196,7 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
     const int row_bytes = p.ld * 4;
     // rows per stage: ~32 KB, a multiple of the rows the CTA covers per pass
     int RB = (32 * 1024) / row_bytes;
-    constexpr int U = (DVW <= 2) ? 4 : (DVW <= 8 ? 2 : 1);
+    constexpr int U = (DVW == 1) ? 8 : (DVW == 2) ? 4 : (DVW <= 8 ? 2 : 1);
     const int pass = GD_CONSUMER_WARPS * RPW * U;
     if (RB < pass) RB = pass;
     RB = RB / pass * pass;
@@ -231,11 +231,12 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
 }
 
 int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
+    // narrow rows: few lanes per row (several rows per warp instruction), wide rows: the whole warp per row
     if (p.ld <= 32) return launch_rw<8, 1>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 64) return launch_rw<16, 1>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 128) return launch_rw<32, 1>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 256) return launch_rw<32, 2>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 512) return launch_rw<32, 4>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 64) return launch_rw<8, 2>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 128) return launch_rw<8, 4>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 256) return launch_rw<8, 8>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 512) return launch_rw<16, 8>(p, d_scratch, scratch_bytes, stream);
     if (p.ld <= 1024) return launch_rw<32, 8>(p, d_scratch, scratch_bytes, stream);
     return launch_rw<32, 16>(p, d_scratch, scratch_bytes, stream);
 }
