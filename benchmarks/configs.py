@@ -183,12 +183,12 @@ def bench_latency(ctx, a):
     """Protocol cost of one round: tiny data, no injected delay (launch + flags + NVLink ship + decode + push)."""
     for scheme, s, k in (("approx", 1, 4), ("coded", 2, 0), ("naive", 0, 0)):
         cfg = mkcfg(scheme, 8, s, 8 * 256, 4096, k=k, rounds=260, synthetic=True, seed=1, add_delay=0,
-                    beta_push=a.beta_push)
+                    beta_push=a.beta_push, cuda_graph=a.cuda_graph)
         eng = Engine(cfg, None, ctx=ctx)
         ms = timed_rounds(ctx, eng, 20, 200)
         emit(ctx, {"config": "round_latency", "scheme": scheme, "gpus": ctx.world, "n_workers": 8, "d": 4096,
                    "rows_per_partition": 256, "us_per_round": ms * 1e3, "message_bytes": 4096 * 4,
-                   "beta_push": a.beta_push,
+                   "beta_push": a.beta_push, "cuda_graph": a.cuda_graph,
                    "kernels_per_round_rank0": eng.launches_per_round()})
         eng.close()
 
@@ -203,6 +203,7 @@ if __name__ == "__main__":
     ap.add_argument("--rows-sweep", type=int, default=32768)
     ap.add_argument("--eta0", type=float, default=10.0)
     ap.add_argument("--beta-push", default="p2p")
+    ap.add_argument("--cuda-graph", action="store_true")
     a = ap.parse_args()
     ctx = init_distributed()
     which = a.only.split(",")

@@ -108,3 +108,37 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
     }
     return EH_OK;
 }
+
+extern "C" int eh_run_rounds_graph(const eh_round_plan* plan, int first_round, int n_rounds, int r0, void* stream,
+                                   void** graph_exec) {
+    using namespace eh;
+    EH_REQUIRE(graph_exec, "run_rounds_graph: null output");
+    cudaStream_t st = (cudaStream_t)stream;
+    EH_REQUIRE(st != nullptr, "run_rounds_graph: capture needs a non-default stream");
+    *graph_exec = nullptr;
+    EH_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
+    const int rc = eh_run_rounds(plan, first_round, n_rounds, r0, stream);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(st, &graph);
+    if (rc != EH_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    EH_CUDA(e);
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    EH_CUDA(ei);
+    const cudaError_t el = cudaGraphLaunch(exec, st);
+    if (el != cudaSuccess) {
+        cudaGraphExecDestroy(exec);
+        EH_CUDA(el);
+    }
+    *graph_exec = (void*)exec;
+    return EH_OK;
+}
+
+extern "C" int eh_graph_destroy(void* graph_exec) {
+    if (graph_exec) EH_CUDA(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+    return EH_OK;
+}

@@ -102,6 +102,7 @@ class RunConfig:
     metrics_jsonl: Optional[str] = None
     decode: str = "auto"                   # auto | table | solve
     quiet: bool = False
+    cuda_graph: bool = False               # capture each enqueue of rounds into one CUDA graph
     beta_push: str = "p2p"                 # parameter broadcast: p2p (peer stores) | multicast (NVLS multimem.st)
     dtype: str = "fp32"                    # storage of dense features on the GPU: fp32 | bf16 (half the HBM traffic)
     debug_poison: bool = False             # fill every message slot with NaN before a run (stale-read detector)

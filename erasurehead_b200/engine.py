@@ -331,8 +331,22 @@ class Engine:
         """Enqueue ``n_rounds`` further rounds on the current stream (no synchronisation)."""
         from .ops import _lib
         r0 = self._cursor - self.first_round
-        _lib.check(_lib.lib().eh_run_rounds(C.byref(self.plan), self._cursor, n_rounds, r0, _lib.stream_ptr()),
-                   "eh_run_rounds")
+        if self.cfg.cuda_graph:
+            # one graph for all n_rounds rounds, launched on a side stream (capture needs a real stream)
+            torch = self.torch
+            if not hasattr(self, "_graph_stream"):
+                self._graph_stream = torch.cuda.Stream()
+                self._graphs = []
+            self._graph_stream.wait_stream(torch.cuda.current_stream())
+            exec_ = C.c_void_p()
+            _lib.check(_lib.lib().eh_run_rounds_graph(C.byref(self.plan), self._cursor, n_rounds, r0,
+                                                      self._graph_stream.cuda_stream, C.byref(exec_)),
+                       "eh_run_rounds_graph")
+            self._graphs.append(exec_)
+            torch.cuda.current_stream().wait_stream(self._graph_stream)
+        else:
+            _lib.check(_lib.lib().eh_run_rounds(C.byref(self.plan), self._cursor, n_rounds, r0, _lib.stream_ptr()),
+                       "eh_run_rounds")
         self._cursor += n_rounds
         self.launches += n_rounds * self.launches_per_round()
 
@@ -372,6 +386,11 @@ class Engine:
 
     def finish(self) -> None:
         self.torch.cuda.synchronize()
+        for g in getattr(self, "_graphs", []):
+            from .ops import _lib
+            _lib.lib().eh_graph_destroy(g)
+        if hasattr(self, "_graphs"):
+            self._graphs = []
         err = self.ws.error()
         errs = self.ctx.all_gather_object(err)
         if any(errs):

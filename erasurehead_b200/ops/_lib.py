@@ -140,6 +140,8 @@ def _declare(lib):
         "eh_decoder_round": (i32, [P(DecoderDesc), i32, i32, vp]),
         "eh_decoder_publish": (i32, [P(DecoderDesc), i32, vp]),
         "eh_run_rounds": (i32, [P(RoundPlan), i32, i32, i32, vp]),
+        "eh_run_rounds_graph": (i32, [P(RoundPlan), i32, i32, i32, vp, P(vp)]),
+        "eh_graph_destroy": (i32, [vp]),
         "eh_margins_dense": (i32, [vp, i64, i32, i32, vp, i32, i32, vp, vp]),
         "eh_margins_ell": (i32, [vp, i64, i32, vp, i32, i32, vp, vp]),
         "eh_eval_tc": (i32, [vp, i64, i32, i32, vp, i32, i32, vp, i32, vp, vp, i32, vp]),

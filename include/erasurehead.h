@@ -256,6 +256,13 @@ typedef struct eh_round_plan {
 
 /* r0 = index of `first_round` in the decoder's per-round tables. */
 int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_rounds, int r0, void* stream);
+/* Same work captured into ONE CUDA graph (stream capture of the enqueue above) and launched once:
+ * the host pays one graph launch instead of n_rounds * kernels-per-round launches and the kernels of
+ * consecutive rounds are dependency-linked on the device.  *graph_exec receives the instantiated
+ * graph; release it with eh_graph_destroy after the stream has been synchronised. */
+int eh_run_rounds_graph(const eh_round_plan* plan, int first_round, int n_rounds, int r0, void* stream,
+                        void** graph_exec);
+int eh_graph_destroy(void* graph_exec);
 
 /* ------------------------------------------------------------------------------------------
  * Evaluation (reference epilogue naive.py:154-209, util.py:136-141, sklearn roc_curve+auc).

@@ -243,3 +243,14 @@ def test_engine_bf16_storage_matches_oracle_on_rounded_data():
     ev = eng.evaluate(res)
     assert np.all(np.isfinite(ev.training_loss))
     eng.close()
+
+
+def test_cuda_graph_mode_matches_stream_mode():
+    """The whole run captured into one CUDA graph gives the same trajectory."""
+    for scheme, kw in (("approx", dict(s=1, k=5)), ("coded", dict(s=2, seed=3)), ("partial_coded", dict(n=4, s=1, P=4, rows=12 * 160, seed=2))):
+        cfg = mk(scheme, **kw)
+        data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=1)
+        dl = spaced_delays(cfg.rounds, cfg.n_workers, seed=5)
+        a = Engine(cfg, data, delays=dl); ra = a.run(); a.close()
+        b = Engine(cfg.replace(cuda_graph=True), data, delays=dl); rb = b.run(); b.close()
+        assert np.array_equal(ra.betaset, rb.betaset) and np.array_equal(ra.n_collected, rb.n_collected)
