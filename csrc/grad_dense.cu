@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
     unsigned char* stages = smem_raw;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)p.n_stages * stage_bytes);
     uint64_t* empty = full + GD_MAX_STAGES;
-    float* red = reinterpret_cast<float*>(empty + GD_MAX_STAGES);      // [2][8][RB]
+    float* red = reinterpret_cast<float*>(empty + GD_MAX_STAGES);      // [2][RB][8], 16-byte aligned
     __shared__ uint32_t s_decision;
 
     const JobView jv = job_of_cta(p);
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
             for (long long k = issued; k < my_steps; ++k) {
                 const int st = (int)(k % p.n_stages);
                 const uint32_t use = (uint32_t)(k / p.n_stages);      // >= 1 here
-                mbar_wait(&empty[st], (use - 1) & 1);
+                mbar_wait_backoff(&empty[st], (use - 1) & 1);
                 issue(k);
             }
         }
@@ -124,12 +124,14 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
                 bt[v][e] = (c + e < p.d) ? p.beta[c + e] : 0.f;
             }
         }
+        // tile position kept incrementally (no 64-bit divisions in the loop)
+        int sg = jv.seg0 + jv.bl / p.steps_per_seg;
+        int sstep = jv.bl % p.steps_per_seg;
+        int st = 0;
+        uint32_t phase = 0;
+        const bool cols_full = (ldv == DV * GD_CONSUMERS);
         for (long long k = 0; k < my_steps; ++k) {
-            const int st = (int)(k % p.n_stages);
-            const uint32_t use = (uint32_t)(k / p.n_stages);
-            const long long step = jv.bl + k * (long long)jv.Gj;
-            const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
-            const int row0 = (int)(step % p.steps_per_seg) * RB;
+            const int row0 = sstep * RB;
             const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
             // labels / encode weight of this tile (independent of the TMA data)
             const float cf = p.coeff[sg];
@@ -137,47 +139,64 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
             float yv[RB];
 #pragma unroll
             for (int r = 0; r < RB; ++r) yv[r] = (r < nr) ? __ldg(ys + r) : 0.f;
-            mbar_wait(&full[st], use & 1);
+            mbar_wait(&full[st], phase);
             const uint4* tile = reinterpret_cast<const uint4*>(stages + (size_t)st * stage_bytes);
             float x[RB][DV][E];
             float dot[RB];
+            if (nr == RB && cols_full) {
+                // full tile: no per-element predicates
 #pragma unroll
-            for (int r = 0; r < RB; ++r) {
-                dot[r] = 0.f;
+                for (int r = 0; r < RB; ++r) {
+                    dot[r] = 0.f;
 #pragma unroll
-                for (int v = 0; v < DV; ++v) {
-                    const int cv = v * GD_CONSUMERS + tid;
-                    uint4 q = make_uint4(0u, 0u, 0u, 0u);
-                    if (r < nr && cv < ldv) q = tile[(size_t)r * ldv + cv];
-                    unpack16<E>(q, x[r][v]);
+                    for (int v = 0; v < DV; ++v) {
+                        unpack16<E>(tile[(size_t)r * ldv + v * GD_CONSUMERS + tid], x[r][v]);
 #pragma unroll
-                    for (int e = 0; e < E; ++e) dot[r] = fmaf(x[r][v][e], bt[v][e], dot[r]);
+                        for (int e = 0; e < E; ++e) dot[r] = fmaf(x[r][v][e], bt[v][e], dot[r]);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < RB; ++r) {
+                    dot[r] = 0.f;
+#pragma unroll
+                    for (int v = 0; v < DV; ++v) {
+                        const int cv = v * GD_CONSUMERS + tid;
+                        uint4 q = make_uint4(0u, 0u, 0u, 0u);
+                        if (r < nr && cv < ldv) q = tile[(size_t)r * ldv + cv];
+                        unpack16<E>(q, x[r][v]);
+#pragma unroll
+                        for (int e = 0; e < E; ++e) dot[r] = fmaf(x[r][v][e], bt[v][e], dot[r]);
+                    }
                 }
             }
 #pragma unroll
             for (int r = 0; r < RB; ++r) dot[r] = warp_sum(dot[r]);
             // all lanes' tile reads are complete (their values fed the shuffles): free the slot
-            float* redw = red + ((k & 1) * GD_CONSUMER_WARPS + warp) * RB;
+            float* redk = red + (k & 1) * GD_CONSUMER_WARPS * RB;             // [RB][8 warps]
             if (lane == 0) {
 #pragma unroll
-                for (int r = 0; r < RB; ++r) redw[r] = dot[r];
+                for (int r = 0; r < RB; ++r) redk[r * GD_CONSUMER_WARPS + warp] = dot[r];
                 mbar_arrive(&empty[st]);
             }
             asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
-            const float* redk = red + (k & 1) * GD_CONSUMER_WARPS * RB;
+            const float4* red4 = reinterpret_cast<const float4*>(redk);
 #pragma unroll
             for (int r = 0; r < RB; ++r) {
-                if (r < nr) {
-                    float pr = 0.f;
+                // rows past the end of a partial tile carry x = 0, y = 0: their residual is finite and
+                // multiplies zeros, so no predicate is needed here
+                const float4 a = red4[r * 2], b = red4[r * 2 + 1];
+                const float pr = ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+                const float rs = cf * residual(p.model, pr, yv[r]);
 #pragma unroll
-                    for (int w = 0; w < GD_CONSUMER_WARPS; ++w) pr += redk[w * RB + r];
-                    const float rs = cf * residual(p.model, pr, yv[r]);
+                for (int v = 0; v < DV; ++v)
 #pragma unroll
-                    for (int v = 0; v < DV; ++v)
-#pragma unroll
-                        for (int e = 0; e < E; ++e) acc[v][e] = fmaf(rs, x[r][v][e], acc[v][e]);
-                }
+                    for (int e = 0; e < E; ++e) acc[v][e] = fmaf(rs, x[r][v][e], acc[v][e]);
             }
+            // next tile of this CTA
+            if (++st == p.n_stages) { st = 0; phase ^= 1u; }
+            sstep += jv.Gj;
+            while (sstep >= p.steps_per_seg) { sstep -= p.steps_per_seg; ++sg; }
         }
         // ---------------- per-CTA partial -> scratch (fp32)
         float4* mine = reinterpret_cast<float4*>(p.partials + (size_t)blockIdx.x * p.ldp);

@@ -141,7 +141,8 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
 
 // Parameter-flag wait by CTA 0 and broadcast of the go/skip decision to the other CTAs.
 // Called by one thread per CTA; returns DEC_GO or DEC_SKIP.
-__device__ __forceinline__ uint32_t wait_for_parameters(const GradParams& p) {
+template <class Params>
+__device__ __forceinline__ uint32_t wait_for_parameters(const Params& p) {
     uint32_t code = DEC_GO;
     if (blockIdx.x == 0) {
         if (p.beta_flag) {

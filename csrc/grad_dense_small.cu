@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             for (long long k = issued; k < my_steps; ++k) {
                 const int st = (int)(k % p.n_stages);
                 const uint32_t use = (uint32_t)(k / p.n_stages);
-                mbar_wait(&empty[st], (use - 1) & 1);
+                mbar_wait_backoff(&empty[st], (use - 1) & 1);
                 issue(k);
             }
         }

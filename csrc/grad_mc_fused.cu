@@ -1,0 +1,475 @@
+// One-pass multi-column gradient: both products of  G = X^T . resid(X . W^T)  from ONE shared
+// memory copy of each X tile (SURVEY 7.4 hard part 2), in a single launch that also waits for the
+// round's parameters, reduces across CTAs in a fixed order and ships the message.
+//
+//   tile = 128 rows x dk columns, resident in a ring of 64 KB "super-stages" (128 rows x 128 columns,
+//   four TMA boxes of 128 x 32 fp32, 32B-atom 128B swizzle = the layout the MN-major tf32 operand of
+//   tcgen05.mma requires);
+//   forward   P = X . W^T  on the legacy warp-level tensor-core path (mma.sync m16n8k8 tf32): the
+//             K-major use of a 32B-atom-swizzled tile is not expressible as a tcgen05 descriptor
+//             ("SWIZZLE_128B_BASE32B is invalid for Major-K"), while warps can read any layout; the
+//             product is tiny (N = 8..32 columns) and its result lands in registers where the
+//             softmax / logistic residual needs it;
+//   residual  R = coeff * (softmax(P) - onehot(y))  or  coeff * -y / (exp(P y) + 1), rounded to
+//             tf32 and written to shared memory in the K-major SW128 operand layout;
+//   backward  G[j, c] += sum_r X[r, j] R[r, c]: tcgen05.mma kind::tf32, A = the same X tile read
+//             MN-major (M = 128 feature columns, K = 8 rows per instruction), accumulators for all
+//             column chunks in TMEM for the CTA's whole row range; the commit of the last MMA that
+//             reads a super-stage releases it to the TMA producer;
+//   tail      TMEM -> per-CTA partial in scratch, device-wide barrier, fixed-order reduction,
+//             store into the (peer-mapped) destination, release flag.
+//
+// Handles dk <= 128 * ring slots that fit next to W and R in shared memory (dk <= 256 for 16
+// columns, 384 for 8); wider problems use the two-pass tcgen05 kernels of grad_mc_tc.cu.
+// No counterpart in the reference (its models are single vectors, naive.py:137-139).
+#include <stdlib.h>
+
+#include "grad_dense.cuh"
+#include "tc_common.cuh"
+
+namespace eh {
+
+constexpr int MF_BOX_BYTES = 128 * 32 * 4;            // one TMA box: 128 rows x 32 columns
+constexpr int MF_STAGE_BYTES = 4 * MF_BOX_BYTES;      // super-stage: 128 rows x 128 columns
+constexpr int MF_MAX_STAGES = 3;
+constexpr int MF_COMPUTE = 256;                      // 8 compute warps (16 tile rows each)
+constexpr int MF_THREADS = 128 + MF_COMPUTE;          // + TMA producer, MMA issuer, TMEM allocator, spare
+
+struct McFusedMaps {
+    CUtensorMap x[EH_MAX_SEGS];
+};
+
+struct McFusedParams {
+    const float* seg_y[EH_MAX_SEGS];
+    float coeff[EH_MAX_SEGS];
+    const float* W;                  // [CN, ldw]
+    float* out;                      // [CN, ldw] destination (local or peer)
+    uint32_t* flag;
+    const uint32_t* beta_flag;
+    uint32_t* err;
+    GradScratchHdr* hdr;
+    float* partials;                 // [grid][CN * ldw]
+    int n_segs, rows_per_seg, tiles_per_seg;
+    int d, dk, ldw, n_chunks, C, model, n_stages;
+    int w_stride;                    // floats between consecutive column pairs of the W image
+    uint32_t stamp, seq;
+    unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mma_tf32_16x8x8(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                uint32_t b0, uint32_t b1) {
+    asm(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// NBC = 8-column blocks of the model (BN = 8 * NBC columns in the tensor-core tiles)
+template <int NBC>
+__global__ void __launch_bounds__(MF_THREADS, 1)
+mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p) {
+    constexpr int BN = 8 * NBC;
+    constexpr int R_BYTES = 4 * BN * 128;             // four K-major sub-tiles [BN x 32 rows]
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* ring = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* Rs = ring + (size_t)p.n_stages * MF_STAGE_BYTES;
+    float* Ws = reinterpret_cast<float*>(Rs + R_BYTES);                     // [dk/2][w_stride] column pairs
+    uint64_t* full = reinterpret_cast<uint64_t*>(Ws + (size_t)(p.dk / 2) * p.w_stride);
+    uint64_t* empty = full + MF_MAX_STAGES;
+    uint64_t* rfull = empty + MF_MAX_STAGES;
+    uint64_t* rempty = rfull + 1;
+    uint64_t* tdone = rempty + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tdone + 1);
+    volatile uint32_t& s_decision = *(tmem_slot + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int G = gridDim.x;
+    const int n_tiles = p.n_segs * p.tiles_per_seg;
+    const int my_tiles = ((int)blockIdx.x < n_tiles) ? (n_tiles - (int)blockIdx.x + G - 1) / G : 0;
+    const int my_items = my_tiles * p.n_chunks;
+    constexpr uint32_t TMEM_COLS = 128;
+
+    if (tid == 0) {
+        for (int s = 0; s < MF_MAX_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(rfull, MF_COMPUTE / 32);
+        mbar_init(rempty, 1);
+        mbar_init(tdone, 1);
+        mbar_fence_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // box loads of one (tile, chunk) item into its ring slot
+    auto issue = [&](int it, uint64_t pol) {
+        const int tl = it / p.n_chunks, ch = it % p.n_chunks;
+        const int T = (int)blockIdx.x + tl * G;
+        const int sg = T / p.tiles_per_seg, row0 = (T % p.tiles_per_seg) * 128;
+        const int st = it % p.n_stages;
+        int nb = (p.dk - ch * 128 + 31) / 32;
+        if (nb > 4) nb = 4;
+        unsigned char* dst = ring + (size_t)st * MF_STAGE_BYTES;
+        mbar_arrive_expect_tx(&full[st], (uint32_t)nb * MF_BOX_BYTES);
+        for (int bx = 0; bx < nb; ++bx)
+            tma_load_2d(dst + bx * MF_BOX_BYTES, &maps.x[sg], ch * 128 + bx * 32, row0, &full[st], pol);
+    };
+
+    uint32_t code = DEC_GO;
+    if (warp == 0) {
+        // ---------------- TMA producer; prefetches X while the parameters are still in flight
+        int issued = 0;
+        const uint64_t pol = l2_policy_evict_first();
+        if (lane == 0) {
+            const int pre = my_items < p.n_stages ? my_items : p.n_stages;
+            for (; issued < pre; ++issued) issue(issued, pol);
+            code = wait_for_parameters(p);
+            s_decision = code;
+        }
+        __syncwarp();
+        asm volatile("bar.sync 1, %0;" ::"r"(MF_THREADS) : "memory");
+        code = s_decision;
+        if (lane == 0) {
+            if (code == DEC_SKIP) {
+                for (int k = 0; k < issued; ++k) mbar_wait(&full[k % p.n_stages], 0);
+            } else {
+                for (int it = issued; it < my_items; ++it) {
+                    mbar_wait_backoff(&empty[it % p.n_stages], ((it / p.n_stages) - 1) & 1);
+                    issue(it, pol);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        asm volatile("bar.sync 1, %0;" ::"r"(MF_THREADS) : "memory");
+        code = s_decision;
+        if (code == DEC_GO && lane == 0) {
+            // ---------------- backward MMA issuer
+            constexpr uint32_t idesc = make_idesc_tf32(128, BN, /*a_mn_major=*/1, /*b_mn_major=*/0);
+            const uint32_t r_addr = smem_u32(Rs);
+            int it = 0;
+            for (int tl = 0; tl < my_tiles; ++tl) {
+                mbar_wait(rfull, tl & 1);
+                tc_fence_after();
+                for (int ch = 0; ch < p.n_chunks; ++ch, ++it) {
+                    const int st = it % p.n_stages;
+                    mbar_wait(&full[st], (it / p.n_stages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(ring + (size_t)st * MF_STAGE_BYTES);
+                    const uint32_t d_tmem = tmem_base + ch * BN;
+#pragma unroll
+                    for (int kk = 0; kk < 16; ++kk) {
+                        // A: X^T, MN-major; 8 rows per MMA = 1024 B, 32-column atoms one box apart
+                        const uint64_t a_desc = make_mnmajor_sw128_32b_desc(a_addr + kk * 1024, MF_BOX_BYTES);
+                        const uint64_t b_desc = make_kmajor_sw128_desc(r_addr + (kk >> 2) * (BN * 128)) + (uint64_t)((kk & 3) * 2);
+                        umma_tf32(d_tmem, a_desc, b_desc, idesc, (tl > 0 || kk > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty[st]);          // slot reusable once these MMAs have read it
+                }
+                umma_commit(rempty);                  // R may be overwritten
+            }
+            umma_commit(tdone);
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        asm volatile("bar.sync 1, %0;" ::"r"(MF_THREADS) : "memory");
+        code = s_decision;
+        if (code == DEC_GO) {
+            const int cw = warp - 4;                   // compute warp 0..7 owns tile rows cw*16 .. cw*16+15
+            const int ct = tid - 128;                  // 0..255
+            const int g = lane >> 2, t = lane & 3;
+            // ---------------- parameters -> shared memory as column pairs, tf32-rounded
+            for (int i = ct; i < (p.dk / 2) * BN; i += MF_COMPUTE) {
+                const int n = i % BN, cp = i / BN;
+                float2 w;
+                w.x = round_tf32(__ldcg(p.W + (size_t)n * p.ldw + 2 * cp));
+                w.y = round_tf32(__ldcg(p.W + (size_t)n * p.ldw + 2 * cp + 1));
+                *reinterpret_cast<float2*>(Ws + (size_t)cp * p.w_stride + 2 * n) = w;
+            }
+            asm volatile("bar.sync 2, %0;" ::"r"(MF_COMPUTE) : "memory");
+
+            // per-thread constants of the fragment addressing (shared-space byte addresses)
+            const uint32_t ring_u = smem_u32(ring), ws_u = smem_u32(Ws), rs_u = smem_u32(Rs);
+            // X rows r0 = cw*16 + g and r0 + 8 (same r & 3): offset inside a box with the 32B-chunk XOR folded in
+            const int r0 = cw * 16 + g;
+            const uint32_t xoff = (uint32_t)r0 * 128u + (uint32_t)t * 8u + ((uint32_t)(r0 & 3) << 5);
+            const uint32_t woff = ws_u + (uint32_t)t * (uint32_t)p.w_stride * 4u + (uint32_t)g * 8u;
+            const uint32_t wstep = (uint32_t)p.w_stride * 16u;           // 4 column pairs = one k-step of 8 columns
+            // R^T image: sub-tile (32 rows) cw/2, row inside it rr = (cw&1)*16 + h*8 + g
+            const int rr0 = (cw & 1) * 16 + g;
+            const uint32_t roff = rs_u + (uint32_t)(cw >> 1) * (BN * 128) + (uint32_t)(rr0 & 3) * 4u;
+
+            int it = 0;
+            for (int tl = 0; tl < my_tiles; ++tl) {
+                const int T = (int)blockIdx.x + tl * G;
+                const int sg = T / p.tiles_per_seg, row0 = (T % p.tiles_per_seg) * 128;
+                const float cf = p.coeff[sg];
+                float yv[2];
+                bool valid[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int r = row0 + r0 + h * 8;
+                    valid[h] = r < p.rows_per_seg;
+                    yv[h] = valid[h] ? __ldg(p.seg_y[sg] + r) : 0.f;
+                }
+                float acc[NBC][4];
+#pragma unroll
+                for (int nb = 0; nb < NBC; ++nb)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) acc[nb][e] = 0.f;
+
+                // ---------------- forward: warp-level tf32 MMAs straight from the swizzled tile
+                for (int ch = 0; ch < p.n_chunks; ++ch, ++it) {
+                    const int st = it % p.n_stages;
+                    mbar_wait(&full[st], (it / p.n_stages) & 1);
+                    const uint32_t stage = ring_u + (uint32_t)st * MF_STAGE_BYTES + xoff;
+                    int nbx = (p.dk - ch * 128 + 31) / 32;
+                    if (nbx > 4) nbx = 4;
+                    uint32_t wp = woff + (uint32_t)(ch * 16) * wstep;
+#pragma unroll
+                    for (int bx = 0; bx < 4; ++bx) {
+                        if (bx < nbx) {
+                            // logical k = t / t+4 of the instruction <-> physical columns 2t / 2t+1
+                            uint2 a[4][2], bfr[4][NBC];
+#pragma unroll
+                            for (int kk = 0; kk < 4; ++kk) {
+                                const uint32_t xa = (stage + bx * MF_BOX_BYTES) ^ ((uint32_t)kk << 5);
+                                a[kk][0] = lds64(xa);
+                                a[kk][1] = lds64(xa + 8 * 128);
+#pragma unroll
+                                for (int nb = 0; nb < NBC; ++nb) bfr[kk][nb] = lds64(wp + (uint32_t)kk * wstep + nb * 64);
+                            }
+#pragma unroll
+                            for (int kk = 0; kk < 4; ++kk)
+#pragma unroll
+                                for (int nb = 0; nb < NBC; ++nb)
+                                    mma_tf32_16x8x8(acc[nb], a[kk][0].x, a[kk][1].x, a[kk][0].y, a[kk][1].y, bfr[kk][nb].x,
+                                                    bfr[kk][nb].y);
+                        }
+                        wp += 4 * wstep;
+                    }
+                }
+
+                // ---------------- residual per row (a row's columns live in the 4 lanes of a quad)
+                float res[2][NBC][2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    if (p.model == 2) {
+                        float m = -3.0e38f;
+#pragma unroll
+                        for (int nb = 0; nb < NBC; ++nb)
+#pragma unroll
+                            for (int j = 0; j < 2; ++j)
+                                if (nb * 8 + 2 * t + j < p.C) m = fmaxf(m, acc[nb][2 * h + j]);
+                        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+                        float sum = 0.f;
+#pragma unroll
+                        for (int nb = 0; nb < NBC; ++nb)
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const float e = (nb * 8 + 2 * t + j < p.C) ? __expf(acc[nb][2 * h + j] - m) : 0.f;
+                                res[h][nb][j] = e;
+                                sum += e;
+                            }
+                        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+                        const float inv = __fdividef(1.f, sum);
+                        const int yc = (int)yv[h];
+#pragma unroll
+                        for (int nb = 0; nb < NBC; ++nb)
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const int n = nb * 8 + 2 * t + j;
+                                const float r = cf * (res[h][nb][j] * inv - (n == yc ? 1.f : 0.f));
+                                res[h][nb][j] = valid[h] ? round_tf32(r) : 0.f;
+                            }
+                    } else {
+#pragma unroll
+                        for (int nb = 0; nb < NBC; ++nb)
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const int n = nb * 8 + 2 * t + j;
+                                const float z = acc[nb][2 * h + j] * yv[h];
+                                const float r = cf * __fdividef(-yv[h], __expf(z) + 1.0f);
+                                res[h][nb][j] = (valid[h] && n < p.C) ? round_tf32(r) : 0.f;
+                            }
+                    }
+                }
+                // ---------------- R^T into the K-major SW128 operand image
+                if (tl > 0) mbar_wait(rempty, (tl - 1) & 1);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int c16 = (rr0 + h * 8) >> 2;                   // 16-byte chunk of the row inside the sub-tile
+#pragma unroll
+                    for (int nb = 0; nb < NBC; ++nb)
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            const int n = nb * 8 + 2 * t + j;
+                            sts32(roff + (uint32_t)n * 128u + (uint32_t)((c16 ^ (n & 7)) << 4), res[h][nb][j]);
+                        }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(rfull);
+            }
+
+            // ---------------- accumulators: TMEM -> this CTA's partial [CN][ldw]
+            // warp w may touch TMEM lanes 32*(w%4)..+31; the two warps of a lane quarter split the columns
+            float* mine = p.partials + (size_t)blockIdx.x * ((size_t)BN * p.ldw);
+            if (my_tiles > 0) {
+                mbar_wait(tdone, 0);
+                tc_fence_after();
+            }
+            const int q = cw & 3, half = cw >> 2;
+            for (int ch = 0; ch < p.n_chunks; ++ch) {
+                const int j = ch * 128 + q * 32 + lane;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + ch * BN;
+#pragma unroll
+                for (int cbi = 0; cbi < BN / 16; ++cbi) {
+                    const int cb = half * (BN / 16) + cbi;
+                    float v[8];
+                    if (my_tiles > 0) {
+                        uint32_t r[8];
+                        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                                     : "r"(taddr + cb * 8)
+                                     : "memory");
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[e]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) v[e] = 0.f;
+                    }
+                    if (j < p.ldw) {
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) __stcg(mine + (size_t)(cb * 8 + e) * p.ldw + j, (j < p.d) ? v[e] : 0.f);
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    } else {
+        asm volatile("bar.sync 1, %0;" ::"r"(MF_THREADS) : "memory");
+        code = s_decision;
+    }
+
+    // ---------------- common tail
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+    if (code == DEC_SKIP) return;
+
+    uint32_t gen = 0;
+    grid_barrier(&p.hdr->barrier, gen);
+    // fixed-order reduction over the CTAs' partials, straight into the destination
+    const int n4 = (BN * p.ldw) >> 2;
+    for (int i4 = (int)blockIdx.x * MF_THREADS + tid; i4 < n4; i4 += G * MF_THREADS) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4* src = reinterpret_cast<const float4*>(p.partials) + i4;
+        if ((i4 * 4) % p.ldw < p.n_chunks * 128) {         // columns past the last chunk were never written
+#pragma unroll 8
+            for (int b = 0; b < G; ++b) {
+                const float4 v = __ldcg(src + (size_t)b * n4);
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+        }
+        reinterpret_cast<float4*>(p.out)[i4] = s;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence_system();
+        const uint32_t old = atom_add_acq_rel_gpu(&p.hdr->done, 1u);
+        if (old == (uint32_t)G - 1) {
+            p.hdr->barrier = 0;
+            p.hdr->done = 0;
+            __threadfence_system();
+            if (p.flag) st_relaxed_sys(p.flag, p.stamp);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ host
+static size_t mc_fused_smem(int dk, int BN, int stages) {
+    const size_t w_stride = 2 * BN + 16;
+    return 1024 + (size_t)stages * MF_STAGE_BYTES + (size_t)4 * BN * 128 + (size_t)(dk / 2) * w_stride * sizeof(float) +
+           (2 * MF_MAX_STAGES + 3) * sizeof(uint64_t) + 16;
+}
+
+// ring slots for this shape, 0 when the one-pass kernel cannot hold a whole tile
+int mc_fused_stages(int dk, int CN) {
+    const int n_chunks = (dk + 127) / 128;
+    for (int s = MF_MAX_STAGES; s >= n_chunks && s >= 1; --s)
+        if (mc_fused_smem(dk, CN, s) <= (size_t)227 * 1024) return s;
+    return 0;
+}
+
+size_t mc_fused_scratch_bytes(int d, int CN) {
+    const size_t ldw = (size_t)(d + 31) / 32 * 32;
+    int sm = dev_info().sm_count;
+    if (sm <= 0) sm = 160;
+    return sizeof(GradScratchHdr) + (size_t)sm * CN * ldw * sizeof(float);
+}
+
+template <int NBC>
+static int launch_fused(const McFusedMaps& maps, McFusedParams& p, int grid, cudaStream_t st) {
+    const size_t smem = mc_fused_smem(p.dk, 8 * NBC, p.n_stages);
+    auto kern = mc_fused_kernel<NBC>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_done = true;
+    }
+    void* args[] = {(void*)&maps, (void*)&p};
+    return launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(MF_THREADS), args, smem, st);
+}
+
+// `fused_scratch` points at a zero-initialised GradScratchHdr followed by the per-CTA partials.
+int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st) {
+    const int CN = j->C <= 16 ? 16 : 32;
+    const int dk = (j->d + 31) / 32 * 32;
+    McFusedMaps maps;
+    McFusedParams p;
+    memset(&p, 0, sizeof(p));
+    p.n_stages = mc_fused_stages(dk, CN);
+    EH_REQUIRE(p.n_stages > 0, "grad_mc: one-pass kernel cannot hold %d columns", dk);
+    for (int sg = 0; sg < j->n_segs; ++sg) {
+        EH_REQUIRE(j->d_X[sg] && j->d_y[sg], "grad_mc: null segment %d", sg);
+        EH_REQUIRE(((uintptr_t)j->d_X[sg] % 16) == 0, "grad_mc: X must be 16-byte aligned");
+        int rc = make_map(&maps.x[sg], j->d_X[sg], (uint64_t)dk, (uint64_t)j->rows_per_seg, (uint64_t)j->ld, 128, 32,
+                          CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+        if (rc) return rc;
+        p.seg_y[sg] = j->d_y[sg];
+        p.coeff[sg] = j->coeff[sg];
+    }
+    for (int sg = j->n_segs; sg < EH_MAX_SEGS; ++sg) maps.x[sg] = maps.x[0];
+    p.W = j->d_W; p.out = j->d_out; p.flag = j->d_flag; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
+    p.n_segs = j->n_segs; p.rows_per_seg = j->rows_per_seg; p.tiles_per_seg = (j->rows_per_seg + 127) / 128;
+    p.d = j->d; p.dk = dk; p.ldw = j->ldw; p.n_chunks = (dk + 127) / 128; p.C = j->C; p.model = j->model;
+    p.w_stride = 2 * CN + 16;
+    p.stamp = j->stamp; p.seq = next_launch_seq();
+    p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
+    const long long n_tiles = (long long)p.n_segs * p.tiles_per_seg;
+    long long grid = dev_info().sm_count;
+    if (grid > n_tiles) grid = n_tiles;
+    const size_t need = sizeof(GradScratchHdr) + (size_t)grid * CN * p.ldw * sizeof(float);
+    EH_REQUIRE(fused_bytes >= need, "grad_mc: scratch too small for the one-pass kernel (%zu < %zu)", fused_bytes, need);
+    p.hdr = reinterpret_cast<GradScratchHdr*>(fused_scratch);
+    p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(fused_scratch) + sizeof(GradScratchHdr));
+    return CN == 16 ? launch_fused<2>(maps, p, (int)grid, st) : launch_fused<4>(maps, p, (int)grid, st);
+}
+
+}  // namespace eh

@@ -16,6 +16,8 @@
 // Parameters, gradients and messages use the class-major layout W[c][j] (ldw = d padded to 32),
 // which is K-major for the forward product, so the decoder treats a C-column model as one flat
 // vector of CN * ldw entries.  No counterpart in the reference (its models are single vectors).
+#include <stdlib.h>
+
 #include "tc_common.cuh"
 
 namespace eh {
@@ -30,6 +32,7 @@ struct McFwdParams {
     float* Rt;            // [CN, ldr]
     long long ldr;
     double* loss_out;     // [1] summed loss or NULL
+    int a_sw32;           // experiment: X tile stored with the 32B-atom swizzle
 };
 
 template <int NB>
@@ -92,7 +95,7 @@ mc_forward_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constan
                     mbar_wait(&full[st], (it / MC_STAGES) & 1);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(tiles + (size_t)st * STAGE_BYTES);
-                    const uint64_t a_desc = make_kmajor_sw128_desc(a_addr);
+                    const uint64_t a_desc = p.a_sw32 ? make_kmajor_sw128_32b_desc(a_addr) : make_kmajor_sw128_desc(a_addr);
                     const uint64_t b_desc = make_kmajor_sw128_desc(a_addr + TC_A_BYTES);
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 8; ++kk)
@@ -347,13 +350,26 @@ static int launch_bwd(const CUtensorMap& mx, const CUtensorMap& mr, const McBwdP
     return EH_OK;
 }
 
-}  // namespace eh
+// one-pass kernel (grad_mc_fused.cu)
+int mc_fused_stages(int dk, int CN);
+size_t mc_fused_scratch_bytes(int d, int CN);
+int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
 
-extern "C" size_t eh_grad_mc_scratch_bytes(int64_t rows_per_seg, int d, int C) {
-    const int CN = C <= 16 ? 16 : 32;
+static size_t mc_twopass_scratch_bytes(int64_t rows_per_seg, int d, int CN) {
     const int64_t ldr = (rows_per_seg + 31) / 32 * 32;
     const int64_t ldw = (d + 31) / 32 * 32;
-    return (size_t)(CN * ldr + CN * ldw) * sizeof(float) + 1024;
+    return ((size_t)(CN * ldr + CN * ldw) * sizeof(float) + 1024 + 511) / 512 * 512;
+}
+
+}  // namespace eh
+
+// Layout: [two-pass region: Rt, G, skip word][one-pass region: barrier header, per-CTA partials].
+// The one-pass header must start out zero (callers allocate the scratch zero-filled).
+extern "C" size_t eh_grad_mc_scratch_bytes(int64_t rows_per_seg, int d, int C) {
+    const int CN = C <= 16 ? 16 : 32;
+    size_t b = eh::mc_twopass_scratch_bytes(rows_per_seg, d, CN);
+    if (eh::mc_fused_stages((d + 31) / 32 * 32, CN) > 0) b += eh::mc_fused_scratch_bytes(d, CN);
+    return b;
 }
 
 extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
@@ -372,6 +388,11 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
                "grad_mc: d * classes exceeds one CTA's tensor memory (%d chunks x %d columns > 512)", n_chunks, CN);
     EH_REQUIRE(scratch_bytes >= eh_grad_mc_scratch_bytes(j->rows_per_seg, j->d, j->C), "grad_mc: scratch too small");
     cudaStream_t st = (cudaStream_t)stream;
+    // gradient of a narrow model: one pass over X, one launch (grad_mc_fused.cu)
+    if (j->d_out && !j->d_loss && mc_fused_stages(dk, CN) > 0 && getenv("EH_MC_TWOPASS") == nullptr) {
+        const size_t off = mc_twopass_scratch_bytes(j->rows_per_seg, j->d, CN);
+        return mc_fused_launch(j, (char*)d_scratch + off, scratch_bytes - off, st);
+    }
     const long long ldr = ((long long)j->rows_per_seg + 31) / 32 * 32;
     float* Rt = (float*)d_scratch;
     float* G = Rt + (size_t)CN * ldr;
@@ -390,9 +411,12 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
         EH_REQUIRE(((uintptr_t)j->d_X[sg] % 16) == 0, "grad_mc: X must be 16-byte aligned");
         if (j->d_out) EH_CUDA(cudaMemsetAsync(Rt, 0, (size_t)CN * ldr * sizeof(float), st));
         CUtensorMap mx;
-        rc = make_map(&mx, j->d_X[sg], (uint64_t)dk, (uint64_t)j->rows_per_seg, (uint64_t)j->ld, TC_BM);
+        const bool sw32 = getenv("EH_MC_FWD_SW32") != nullptr;
+        rc = make_map(&mx, j->d_X[sg], (uint64_t)dk, (uint64_t)j->rows_per_seg, (uint64_t)j->ld, TC_BM, TC_BK,
+                      sw32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B);
         if (rc) return rc;
         McFwdParams f;
+        f.a_sw32 = sw32 ? 1 : 0;
         f.rows = j->rows_per_seg; f.C = j->C; f.num_k = dk / TC_BK; f.model = j->model; f.coeff = j->coeff[sg];
         f.y = j->d_y[sg]; f.Rt = j->d_out ? Rt : nullptr; f.ldr = ldr; f.loss_out = j->d_loss;
         rc = (NB == 1) ? launch_fwd<1>(mx, mw, f, st) : launch_fwd<2>(mx, mw, f, st);
