@@ -88,6 +88,8 @@ if __name__ == "__main__":
             mc_fused(2097152, 128, 10)
         elif w == "mc_fused256":
             mc_fused(1048576, 256, 16)
+        elif w == "mc_cluster":
+            mc_fused(524288, 1024, 16)
         elif w == "round":
             rounds()
         print("ok", w, flush=True)

@@ -17,6 +17,7 @@
 // which is K-major for the forward product, so the decoder treats a C-column model as one flat
 // vector of CN * ldw entries.  No counterpart in the reference (its models are single vectors).
 #include <stdlib.h>
+#include <string.h>
 
 #include "tc_common.cuh"
 
@@ -354,6 +355,9 @@ static int launch_bwd(const CUtensorMap& mx, const CUtensorMap& mr, const McBwdP
 int mc_fused_stages(int dk, int CN);
 size_t mc_fused_scratch_bytes(int d, int CN);
 int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
+// one-pass kernel on thread-block clusters (grad_mc_cluster.cu)
+bool mc_cluster_plan(int dk, int CN, int* cs_out, int* npc_out, int* stages_out);
+int mc_cluster_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
 
 static size_t mc_twopass_scratch_bytes(int64_t rows_per_seg, int d, int CN) {
     const int64_t ldr = (rows_per_seg + 31) / 32 * 32;
@@ -368,7 +372,9 @@ static size_t mc_twopass_scratch_bytes(int64_t rows_per_seg, int d, int CN) {
 extern "C" size_t eh_grad_mc_scratch_bytes(int64_t rows_per_seg, int d, int C) {
     const int CN = C <= 16 ? 16 : 32;
     size_t b = eh::mc_twopass_scratch_bytes(rows_per_seg, d, CN);
-    if (eh::mc_fused_stages((d + 31) / 32 * 32, CN) > 0) b += eh::mc_fused_scratch_bytes(d, CN);
+    const int dk = (d + 31) / 32 * 32;
+    if (eh::mc_fused_stages(dk, CN) > 0 || eh::mc_cluster_plan(dk, CN, nullptr, nullptr, nullptr))
+        b += eh::mc_fused_scratch_bytes(d, CN);
     return b;
 }
 
@@ -389,9 +395,15 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
     EH_REQUIRE(scratch_bytes >= eh_grad_mc_scratch_bytes(j->rows_per_seg, j->d, j->C), "grad_mc: scratch too small");
     cudaStream_t st = (cudaStream_t)stream;
     // gradient of a narrow model: one pass over X, one launch (grad_mc_fused.cu)
-    if (j->d_out && !j->d_loss && mc_fused_stages(dk, CN) > 0 && getenv("EH_MC_TWOPASS") == nullptr) {
+    if (j->d_out && !j->d_loss && getenv("EH_MC_TWOPASS") == nullptr) {
         const size_t off = mc_twopass_scratch_bytes(j->rows_per_seg, j->d, CN);
-        return mc_fused_launch(j, (char*)d_scratch + off, scratch_bytes - off, st);
+        const char* which = getenv("EH_MC_ONEPASS");            // "cta" | "cluster" force one variant
+        const bool cta_ok = mc_fused_stages(dk, CN) > 0 && !(which && strcmp(which, "cluster") == 0);
+        if (cta_ok) return mc_fused_launch(j, (char*)d_scratch + off, scratch_bytes - off, st);
+        // clusters pay off up to ~1024 columns (1.15-1.2x the two-pass kernels); wider rows only on request
+        const bool cluster_wanted = (which && strcmp(which, "cluster") == 0) || dk <= 1024;
+        if (cluster_wanted && mc_cluster_plan(dk, CN, nullptr, nullptr, nullptr))
+            return mc_cluster_launch(j, (char*)d_scratch + off, scratch_bytes - off, st);
     }
     const long long ldr = ((long long)j->rows_per_seg + 31) / 32 * 32;
     float* Rt = (float*)d_scratch;

@@ -204,11 +204,17 @@ def test_grad_mc_tensor_core_softmax_and_batched_logistic(rows, d, C, model):
 
 
 @pytest.mark.parametrize("rows,d,C,model", [(256, 128, 4, 2), (1000, 200, 7, 2), (777, 96, 20, 2), (1500, 54, 7, 2),
-                                            (90000, 256, 16, 2), (70001, 120, 5, 3), (3000, 384, 3, 3)])
-def test_grad_mc_one_pass_kernel(rows, d, C, model, monkeypatch):
-    """Narrow models take the one-pass kernel (mma.sync forward + tcgen05 backward from one shared
-    memory tile, one launch); it must agree with fp64 torch and with the two-pass kernels."""
+                                            (90000, 256, 16, 2), (70001, 120, 5, 3), (3000, 384, 3, 3),
+                                            (9000, 640, 10, 2), (5000, 1024, 16, 2), (2500, 2048, 24, 2),
+                                            (3333, 4096, 7, 2), (1200, 3000, 12, 3)])
+@pytest.mark.parametrize("variant", ["auto", "cluster"])
+def test_grad_mc_one_pass_kernels(rows, d, C, model, variant, monkeypatch):
+    """One-pass kernels (mma.sync forward + tcgen05 backward from one shared-memory tile, one launch):
+    the single-CTA kernel for narrow models and the thread-block-cluster kernel (column slices per
+    CTA, DSMEM exchange of the partial margins) must agree with fp64 torch and the two-pass kernels."""
     from erasurehead_b200.ops import mc, synth
+    if variant == "cluster":
+        monkeypatch.setenv("EH_MC_ONEPASS", "cluster")
     torch.manual_seed(rows + d + C)
     ld = synth.pad_cols(d)
     Xs, ys = [], []
@@ -223,8 +229,8 @@ def test_grad_mc_one_pass_kernel(rows, d, C, model, monkeypatch):
     cf = [1.0, -0.6, 0.25]
     G, _ = mc.grad_mc(Xs, ys, Wp, d, C, coeff=cf, model=model)
     G2, _ = mc.grad_mc(Xs, ys, Wp, d, C, coeff=cf, model=model)
-    if d <= 256:
-        assert torch.equal(G, G2)                      # one-pass kernel: fixed-order reduction, bitwise repeatable
+    if variant == "cluster" or d <= 1024:             # one-pass kernels: fixed-order reductions, bitwise repeatable
+        assert torch.equal(G, G2)
     want = torch.zeros(d, C, dtype=torch.float64, device=DEV)
     for X, y, c in zip(Xs, ys, cf):
         P = X[:, :d].double() @ W.double()
