@@ -33,7 +33,6 @@ struct McFwdParams {
     float* Rt;            // [CN, ldr]
     long long ldr;
     double* loss_out;     // [1] summed loss or NULL
-    int a_sw32;           // experiment: X tile stored with the 32B-atom swizzle
 };
 
 template <int NB>
@@ -96,7 +95,7 @@ mc_forward_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constan
                     mbar_wait(&full[st], (it / MC_STAGES) & 1);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(tiles + (size_t)st * STAGE_BYTES);
-                    const uint64_t a_desc = p.a_sw32 ? make_kmajor_sw128_32b_desc(a_addr) : make_kmajor_sw128_desc(a_addr);
+                    const uint64_t a_desc = make_kmajor_sw128_desc(a_addr);
                     const uint64_t b_desc = make_kmajor_sw128_desc(a_addr + TC_A_BYTES);
 #pragma unroll
                     for (int kk = 0; kk < TC_BK / 8; ++kk)
@@ -423,12 +422,9 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
         EH_REQUIRE(((uintptr_t)j->d_X[sg] % 16) == 0, "grad_mc: X must be 16-byte aligned");
         if (j->d_out) EH_CUDA(cudaMemsetAsync(Rt, 0, (size_t)CN * ldr * sizeof(float), st));
         CUtensorMap mx;
-        const bool sw32 = getenv("EH_MC_FWD_SW32") != nullptr;
-        rc = make_map(&mx, j->d_X[sg], (uint64_t)dk, (uint64_t)j->rows_per_seg, (uint64_t)j->ld, TC_BM, TC_BK,
-                      sw32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B);
+        rc = make_map(&mx, j->d_X[sg], (uint64_t)dk, (uint64_t)j->rows_per_seg, (uint64_t)j->ld, TC_BM);
         if (rc) return rc;
         McFwdParams f;
-        f.a_sw32 = sw32 ? 1 : 0;
         f.rows = j->rows_per_seg; f.C = j->C; f.num_k = dk / TC_BK; f.model = j->model; f.coeff = j->coeff[sg];
         f.y = j->d_y[sg]; f.Rt = j->d_out ? Rt : nullptr; f.ldr = ldr; f.loss_out = j->d_loss;
         rc = (NB == 1) ? launch_fwd<1>(mx, mw, f, st) : launch_fwd<2>(mx, mw, f, st);

@@ -75,17 +75,6 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
     desc |= (uint64_t)2 << 61;                                 // SWIZZLE_128B
     return desc;
 }
-// K-major view of a tile that was stored with the 32B-atom flavour of the 128B swizzle (the layout the
-// MN-major tf32 operand needs): lets one TMA tile feed both X.W (K-major) and X^T.R (MN-major).
-__device__ __forceinline__ uint64_t make_kmajor_sw128_32b_desc(uint32_t smem_addr) {
-    uint64_t desc = 0;
-    desc |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
-    desc |= (uint64_t)1 << 16;
-    desc |= (uint64_t)(1024 >> 4) << 32;
-    desc |= (uint64_t)1 << 46;
-    desc |= (uint64_t)1 << 61;                                 // SWIZZLE_128B_BASE32B
-    return desc;
-}
 __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_mn_major = 0, int b_mn_major = 0) {
     return (1u << 4)                 // accumulator F32
            | (2u << 7)               // A = TF32
@@ -99,7 +88,8 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_mn_ma
 // layout the tensor core accepts for it is "128B swizzle with 32B atoms" (SWIZZLE_128B_BASE32B,
 // TMA mode CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): atoms of 4 K-rows x 128 B (32 elements along
 // M/N); `lbo_bytes` = distance between consecutive 32-element atoms along M/N, 512 B between
-// consecutive 4-row K groups (rows are 128 B apart).
+// consecutive 4-row K groups (rows are 128 B apart).  This layout is MN-major only: a K-major
+// descriptor over it gives wrong products (tried; CUTLASS: "SWIZZLE_128B_BASE32B is invalid for Major-K").
 __device__ __forceinline__ uint64_t make_mnmajor_sw128_32b_desc(uint32_t smem_addr, uint32_t lbo_bytes) {
     uint64_t desc = 0;
     desc |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
