@@ -8,19 +8,35 @@
 //   ld <=  32 / 64 / 128 / 256 : LPR = 8,  DVW = 1 / 2 / 4 / 8   (4 rows per warp instruction)
 //   ld <=  512                 : LPR = 16, DVW = 8
 //   ld <= 1024 / 2048          : LPR = 32, DVW = 8 / 16
+// bf16 rows (E = 8 columns per 16-byte vector) use the same mapping on half as many vectors.
 #include "grad_dense.cuh"
 
 namespace eh {
 
-template <int LPR, int DVW>
+// 16 bytes of a row as E floats: 4 fp32 values, or 8 bf16 values widened to fp32
+template <int E>
+__device__ __forceinline__ void unpack_vec(const uint4& q, float (&f)[E]) {
+    if constexpr (E == 4) {
+        f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y); f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w);
+    } else {
+        f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
+        f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
+        f[4] = __uint_as_float(q.z << 16); f[5] = __uint_as_float(q.z & 0xffff0000u);
+        f[6] = __uint_as_float(q.w << 16); f[7] = __uint_as_float(q.w & 0xffff0000u);
+    }
+}
+
+// E = columns per 16-byte vector (4 fp32 / 8 bf16), LPR lanes per row, DVW vectors per lane
+template <int E, int LPR, int DVW>
 __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const GradParams p, const int RB) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int RPW = 32 / LPR;                       // rows a warp processes concurrently
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int G = gridDim.x, b = blockIdx.x;
-    const uint32_t stage_bytes = (uint32_t)RB * p.ld * 4u;
-    float* stages = reinterpret_cast<float*>(smem_raw);
+    constexpr int EB = 16 / E;                          // bytes per element
+    const uint32_t stage_bytes = (uint32_t)RB * p.ld * EB;
+    unsigned char* stages = smem_raw;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)p.n_stages * stage_bytes);
     uint64_t* empty = full + GD_MAX_STAGES;
     __shared__ uint32_t s_decision;
@@ -47,11 +63,11 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             const int sg = jv.seg0 + (int)(step / p.steps_per_seg);
             const int row0 = (int)(step % p.steps_per_seg) * RB;
             const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
-            const uint32_t bytes = (uint32_t)nr * p.ld * 4u;
+            const uint32_t bytes = (uint32_t)nr * p.ld * EB;
             const int st = (int)(k % p.n_stages);
             mbar_arrive_expect_tx(&full[st], bytes);
-            tma_load_1d(stages + (size_t)st * RB * p.ld, reinterpret_cast<const float*>(p.seg_X[sg]) + (size_t)row0 * p.ld, bytes,
-                        &full[st], pol);
+            tma_load_1d(stages + (size_t)st * stage_bytes,
+                        reinterpret_cast<const unsigned char*>(p.seg_X[sg]) + (size_t)row0 * p.ld * EB, bytes, &full[st], pol);
         };
         if (lane == 0) {
             const long long pre = my_steps < p.n_stages ? my_steps : p.n_stages;
@@ -82,23 +98,22 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
         if (code == DEC_SKIP) return;
 
         // ---------------- consumers: LPR lanes per row
-        const int ld4 = p.ld >> 2;
+        const int ldv = p.ld / E;                       // 16-byte vectors per row
         const int sub = lane / LPR;                     // which of the warp's concurrent rows
         const int pos = lane % LPR;                     // lane position inside the row
-        float4 bt[DVW], acc[DVW];
+        float bt[DVW][E], acc[DVW][E];
 #pragma unroll
         for (int v = 0; v < DVW; ++v) {
-            const int c = (v * LPR + pos) * 4;
-            acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (c + 0 < p.d) t.x = p.beta[c + 0];
-            if (c + 1 < p.d) t.y = p.beta[c + 1];
-            if (c + 2 < p.d) t.z = p.beta[c + 2];
-            if (c + 3 < p.d) t.w = p.beta[c + 3];
-            bt[v] = t;
+            const int c = (v * LPR + pos) * E;
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+                acc[v][e] = 0.f;
+                bt[v][e] = (c + e < p.d) ? p.beta[c + e] : 0.f;
+            }
         }
         // U rows in flight per lane group: narrow rows are latency-bound (shuffle + exp chain per row)
-        constexpr int U = (DVW == 1) ? 8 : (DVW == 2) ? 4 : (DVW <= 8 ? 2 : 1);
+        constexpr int FL = DVW * E / 4;                 // floats per lane and row, in float4 units
+        constexpr int U = (FL == 1) ? 8 : (FL == 2) ? 4 : (FL <= 8 ? 2 : 1);
         const int rows_per_group = GD_CONSUMER_WARPS * RPW;      // rows the CTA covers per sub-pass
         const int rows_per_pass = rows_per_group * U;
         for (long long k = 0; k < my_steps; ++k) {
@@ -111,9 +126,9 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             const float cf = p.coeff[sg];
             const float* ys = p.seg_y[sg] + row0;
             mbar_wait(&full[st], use & 1);
-            const float4* tile = reinterpret_cast<const float4*>(stages + (size_t)st * RB * p.ld);
+            const uint4* tile = reinterpret_cast<const uint4*>(stages + (size_t)st * stage_bytes);
             for (int r0 = 0; r0 < nr; r0 += rows_per_pass) {
-                float4 x[U][DVW];
+                float x[U][DVW][E];
                 float dot[U], yv[U];
                 bool valid[U];
 #pragma unroll
@@ -124,13 +139,12 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
                     dot[u] = 0.f;
 #pragma unroll
                     for (int v = 0; v < DVW; ++v) {
-                        const int c4 = v * LPR + pos;
-                        x[u][v] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (valid[u] && c4 < ld4) x[u][v] = tile[(size_t)r * ld4 + c4];
-                        dot[u] = fmaf(x[u][v].x, bt[v].x, dot[u]);
-                        dot[u] = fmaf(x[u][v].y, bt[v].y, dot[u]);
-                        dot[u] = fmaf(x[u][v].z, bt[v].z, dot[u]);
-                        dot[u] = fmaf(x[u][v].w, bt[v].w, dot[u]);
+                        const int cv = v * LPR + pos;
+                        uint4 q = make_uint4(0u, 0u, 0u, 0u);
+                        if (valid[u] && cv < ldv) q = tile[(size_t)r * ldv + cv];
+                        unpack_vec<E>(q, x[u][v]);
+#pragma unroll
+                        for (int e = 0; e < E; ++e) dot[u] = fmaf(x[u][v][e], bt[v][e], dot[u]);
                     }
                 }
 #pragma unroll
@@ -142,12 +156,9 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
                 for (int u = 0; u < U; ++u) {
                     const float rs = valid[u] ? cf * residual(p.model, dot[u], yv[u]) : 0.f;
 #pragma unroll
-                    for (int v = 0; v < DVW; ++v) {
-                        acc[v].x = fmaf(rs, x[u][v].x, acc[v].x);
-                        acc[v].y = fmaf(rs, x[u][v].y, acc[v].y);
-                        acc[v].z = fmaf(rs, x[u][v].z, acc[v].z);
-                        acc[v].w = fmaf(rs, x[u][v].w, acc[v].w);
-                    }
+                    for (int v = 0; v < DVW; ++v)
+#pragma unroll
+                        for (int e = 0; e < E; ++e) acc[v][e] = fmaf(rs, x[u][v][e], acc[v][e]);
                 }
             }
             __syncwarp();
@@ -157,20 +168,23 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
 #pragma unroll
         for (int o = LPR; o < 32; o <<= 1) {
 #pragma unroll
-            for (int v = 0; v < DVW; ++v) {
-                acc[v].x += __shfl_xor_sync(0xffffffffu, acc[v].x, o);
-                acc[v].y += __shfl_xor_sync(0xffffffffu, acc[v].y, o);
-                acc[v].z += __shfl_xor_sync(0xffffffffu, acc[v].z, o);
-                acc[v].w += __shfl_xor_sync(0xffffffffu, acc[v].w, o);
-            }
+            for (int v = 0; v < DVW; ++v)
+#pragma unroll
+                for (int e = 0; e < E; ++e) acc[v][e] += __shfl_xor_sync(0xffffffffu, acc[v][e], o);
         }
         asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");      // all tiles consumed: ring is free
+        const int ld4 = p.ld >> 2;
         float4* sacc = reinterpret_cast<float4*>(smem_raw);                    // [8][ld4]
         if (sub == 0) {
 #pragma unroll
             for (int v = 0; v < DVW; ++v) {
-                const int c4 = v * LPR + pos;
-                if (c4 < ld4) sacc[warp * ld4 + c4] = acc[v];
+                const int cv = v * LPR + pos;
+                if (cv < ldv) {
+#pragma unroll
+                    for (int h = 0; h < E / 4; ++h)
+                        sacc[warp * ld4 + cv * (E / 4) + h] =
+                            make_float4(acc[v][4 * h], acc[v][4 * h + 1], acc[v][4 * h + 2], acc[v][4 * h + 3]);
+                }
             }
         }
         asm volatile("bar.sync 2, %0;" ::"r"(GD_CONSUMERS) : "memory");
@@ -189,14 +203,15 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
     reduce_and_ship(p, smem_raw);
 }
 
-template <int LPR, int DVW>
+template <int E, int LPR, int DVW>
 static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
     const DevInfo& di = dev_info();
     constexpr int RPW = 32 / LPR;
-    const int row_bytes = p.ld * 4;
+    const int row_bytes = p.ld * (16 / E);
     // rows per stage: ~32 KB, a multiple of the rows the CTA covers per pass
     int RB = (32 * 1024) / row_bytes;
-    constexpr int U = (DVW == 1) ? 8 : (DVW == 2) ? 4 : (DVW <= 8 ? 2 : 1);
+    constexpr int FL = DVW * E / 4;
+    constexpr int U = (FL == 1) ? 8 : (FL == 2) ? 4 : (FL <= 8 ? 2 : 1);
     const int pass = GD_CONSUMER_WARPS * RPW * U;
     if (RB < pass) RB = pass;
     RB = RB / pass * pass;
@@ -207,12 +222,12 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
     EH_REQUIRE(stages >= 2, "grad_dense: row tile too large for shared memory (ld=%d)", p.ld);
     const size_t tail = 2 * GD_MAX_STAGES * sizeof(uint64_t);
     size_t smem = stages * stage_bytes + tail;
-    const size_t need_red = (size_t)GD_CONSUMER_WARPS * row_bytes;     // sacc + the tail's [8][32] float4
+    const size_t need_red = (size_t)GD_CONSUMER_WARPS * p.ld * sizeof(float);     // sacc + the tail's [8][32] float4
     if (smem < need_red + tail) smem = need_red + tail;
     if (smem < 8 * 32 * sizeof(float4) + tail) smem = 8 * 32 * sizeof(float4) + tail;
     p.n_stages = stages;
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
-    auto kern = grad_dense_rowwarp_kernel<LPR, DVW>;
+    auto kern = grad_dense_rowwarp_kernel<E, LPR, DVW>;
     static bool attr_done = false;
     if (!attr_done) {
         EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
@@ -232,13 +247,21 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
 
 int launch_rowwarp(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t stream) {
     // narrow rows: few lanes per row (several rows per warp instruction), wide rows: the whole warp per row
-    if (p.ld <= 32) return launch_rw<8, 1>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 64) return launch_rw<8, 2>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 128) return launch_rw<8, 4>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 256) return launch_rw<8, 8>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 512) return launch_rw<16, 8>(p, d_scratch, scratch_bytes, stream);
-    if (p.ld <= 1024) return launch_rw<32, 8>(p, d_scratch, scratch_bytes, stream);
-    return launch_rw<32, 16>(p, d_scratch, scratch_bytes, stream);
+    if (p.x_bf16) {
+        if (p.ld <= 64) return launch_rw<8, 8, 1>(p, d_scratch, scratch_bytes, stream);
+        if (p.ld <= 128) return launch_rw<8, 8, 2>(p, d_scratch, scratch_bytes, stream);
+        if (p.ld <= 256) return launch_rw<8, 8, 4>(p, d_scratch, scratch_bytes, stream);
+        if (p.ld <= 512) return launch_rw<8, 16, 4>(p, d_scratch, scratch_bytes, stream);
+        if (p.ld <= 1024) return launch_rw<8, 32, 4>(p, d_scratch, scratch_bytes, stream);
+        return launch_rw<8, 32, 8>(p, d_scratch, scratch_bytes, stream);
+    }
+    if (p.ld <= 32) return launch_rw<4, 8, 1>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 64) return launch_rw<4, 8, 2>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 128) return launch_rw<4, 8, 4>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 256) return launch_rw<4, 8, 8>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 512) return launch_rw<4, 16, 8>(p, d_scratch, scratch_bytes, stream);
+    if (p.ld <= 1024) return launch_rw<4, 32, 8>(p, d_scratch, scratch_bytes, stream);
+    return launch_rw<4, 32, 16>(p, d_scratch, scratch_bytes, stream);
 }
 
 }  // namespace eh

@@ -278,7 +278,8 @@ def test_grad_dense_multi_batches_messages_in_one_launch(d):
     assert torch.allclose(single, outs[1], rtol=1e-4, atol=1e-5)
 
 
-@pytest.mark.parametrize("rows,d", [(200, 64), (1000, 1500), (777, 4096), (300, 8000)])
+@pytest.mark.parametrize("rows,d", [(200, 64), (5000, 100), (3000, 250), (2000, 500), (1000, 1000), (1000, 1500),
+                                    (900, 2048), (777, 4096), (300, 8000)])
 @pytest.mark.parametrize("model", [0, 1])
 def test_grad_dense_bf16_rows(rows, d, model):
     """bf16 feature storage (half the HBM traffic): exact against the reference on the same bf16 values."""
