@@ -6,16 +6,22 @@
 //
 // Reference: scipy CSR matvec + CSR^T matvec in float64 (approximate_coding.py:194-196 with a
 // csr_matrix).  One warp owns a row; the always-on bias column (every row hits it) is summed in
-// registers and added once per warp instead of `rows` colliding atomics.  The accumulation
-// vector lives in `scratch`, zeroed and shipped (to local or peer memory + release flag) by
-// the same cooperative kernel.
+// registers and added once per warp instead of `rows` colliding atomics.  The other popular
+// one-hot values (a categorical column's most frequent level is hit by a large share of the
+// rows) would still serialise as same-address L2 atomics -- ncu showed the Amazon-shaped kernel
+// bound by exactly that -- so every CTA keeps a small direct-mapped table of accumulators in
+// shared memory: a column claims a free slot with a CAS on first use, later hits are shared-memory
+// atomics, slot collisions fall through to the L2 atomic, and the table is flushed with one L2
+// atomic per occupied slot at the end.  The accumulation vector lives in `scratch`, zeroed and
+// shipped (to local or peer memory + release flag) by the same cooperative kernel.
 #include <stdlib.h>
 
 #include "common.cuh"
 
 namespace eh {
 
-constexpr int GE_THREADS = 256;
+constexpr int GE_THREADS = 512;
+constexpr int GE_TABLE = 2048;                 // per-CTA hot-column accumulators (direct-mapped)
 constexpr int GE_MAX_SEGS = EH_MAX_SEGS;
 constexpr uint32_t GE_GO = 1, GE_SKIP = 2;
 
@@ -50,6 +56,9 @@ __device__ __forceinline__ float ell_residual(int model, float p, float y) {
 
 __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p) {
     __shared__ uint32_t s_code;
+    __shared__ int s_tag[GE_TABLE];
+    __shared__ float s_val[GE_TABLE];
+    for (int i = threadIdx.x; i < GE_TABLE; i += GE_THREADS) { s_tag[i] = -1; s_val[i] = 0.f; }
     const int tid = threadIdx.x, lane = tid & 31;
     const int gthreads = gridDim.x * GE_THREADS;
     const int gtid = blockIdx.x * GE_THREADS + tid;
@@ -102,13 +111,29 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
         const float rs = p.coeff[sg] * ell_residual(p.model, s, __ldg(p.seg_y[sg] + lr));
         for (int k = lane; k < p.nnz; k += 32) {
             const int c = __ldg(ri + k);
-            if (c == p.bias_col) bias_acc += rs;
-            else atomicAdd(p.gacc + c, rs);
+            if (c == p.bias_col) {
+                bias_acc += rs;
+            } else {
+                const uint32_t slot = ((uint32_t)c * 2654435761u) >> (32 - 11);
+                int t = s_tag[slot];
+                if (t == -1) {
+                    const int old = atomicCAS(&s_tag[slot], -1, c);
+                    t = (old == -1) ? c : old;
+                }
+                if (t == c) atomicAdd(&s_val[slot], rs);
+                else atomicAdd(p.gacc + c, rs);
+            }
         }
     }
     if (p.bias_col >= 0) {
         bias_acc = warp_sum(bias_acc);
         if (lane == 0 && bias_acc != 0.f) atomicAdd(p.gacc + p.bias_col, bias_acc);
+    }
+    __syncthreads();
+    for (int i = tid; i < GE_TABLE; i += GE_THREADS) {
+        const int t = s_tag[i];
+        const float v = s_val[i];
+        if (t >= 0 && v != 0.f) atomicAdd(p.gacc + t, v);
     }
 
     grid_barrier(&p.hdr->barrier, gen);
@@ -330,7 +355,7 @@ extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scr
     }
     int occ = 0;
     EH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, grad_ell_kernel, GE_THREADS, 0));
-    if (occ > 4) occ = 4;
+    if (occ > 2) occ = 2;                       // fewer, larger CTAs: fewer tables to flush
     if (occ < 1) occ = 1;
     long long want = (p.rows * 32 + GE_THREADS - 1) / GE_THREADS;      // one warp per row
     long long cols = ((long long)j->d + GE_THREADS - 1) / GE_THREADS;
