@@ -30,6 +30,24 @@ from .parallel.context import DistContext, init_distributed
 from .schemes import (DECODE_LSTSQ, MSG_CODED, MSG_PRIVATE, SchemeSpec, build_scheme)
 
 NEVER_NS = (1 << 64) - 1
+
+
+class _nvtx:
+    """NVTX range around an engine phase (shows up in Nsight Systems / ncu --nvtx); no-op on CPU."""
+
+    def __init__(self, engine, name: str):
+        self.on = bool(getattr(engine, "on_gpu", False))
+        self.nvtx = engine.torch.cuda.nvtx if self.on else None
+        self.name = name
+
+    def __enter__(self):
+        if self.on:
+            self.nvtx.range_push(self.name)
+
+    def __exit__(self, *exc):
+        if self.on:
+            self.nvtx.range_pop()
+        return False
 DECODE_TABLE_LIMIT = 50000        # rows of the precomputed decode table (C(n, s))
 
 
@@ -413,13 +431,15 @@ class Engine:
             self.result = res
             self.ctx.barrier()
             return res
-        self.prepare()
+        with _nvtx(self, "eh.prepare"):
+            self.prepare()
         chunk = cfg.checkpoint_every if cfg.checkpoint_every > 0 else R
         done = 0
         while done < R:
             k = min(chunk, R - done)
-            self.enqueue(k)
-            self.finish()
+            with _nvtx(self, f"eh.rounds[{self.first_round + done}:{self.first_round + done + k}]"):
+                self.enqueue(k)
+                self.finish()
             done += k
             if cfg.checkpoint_every > 0 and self.ctx.is_root:
                 self.save_checkpoint(self._ckpt_path(), self.first_round + done)
@@ -449,7 +469,8 @@ class Engine:
             return None
         if not self.on_gpu:
             return results.evaluate_host(self.model, self.data, res.betaset, self._n_eval_parts())
-        return self._evaluate_gpu(res.betaset)
+        with _nvtx(self, "eh.evaluate"):
+            return self._evaluate_gpu(res.betaset)
 
     def _n_eval_parts(self):
         """Q1: the reference evaluates on files 1..n_procs-2 only; None = all partitions."""
