@@ -51,15 +51,19 @@ struct McFusedParams {
     float* partials;                 // [grid][CN * ldw]
     int n_segs, rows_per_seg, tiles_per_seg;
     int d, dk, ldw, n_chunks, C, model, n_stages;
-    int w_stride;                    // floats between consecutive column pairs of the W image
+    int w_stride;                    // floats between consecutive class rows of the W image (dk + 4)
+    int pf;                          // L2 prefetch distance in ring items (0 = off)
+    int n_rbuf;                      // R operand images (2 when shared memory allows: backward of tile t overlaps tile t+1)
     uint32_t stamp, seq;
     unsigned long long timeout_ns;
 };
 
-__device__ __forceinline__ uint2 lds64(uint32_t addr) {
-    uint2 v;
-    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
-    return v;
+// four 8x(16 byte) matrices: lane L supplies the row address of matrix L/8, row L%8; thread T gets the
+// 32-bit word T%4 of row T/4 of each matrix -- exactly the tf32 m16n8k8 fragment order
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(addr));
 }
 __device__ __forceinline__ void sts32(uint32_t addr, float v) {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
@@ -81,12 +85,12 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* ring = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     unsigned char* Rs = ring + (size_t)p.n_stages * MF_STAGE_BYTES;
-    float* Ws = reinterpret_cast<float*>(Rs + R_BYTES);                     // [dk/2][w_stride] column pairs
-    uint64_t* full = reinterpret_cast<uint64_t*>(Ws + (size_t)(p.dk / 2) * p.w_stride);
+    float* Ws = reinterpret_cast<float*>(Rs + p.n_rbuf * R_BYTES);          // [BN][w_stride = dk + 4]
+    uint64_t* full = reinterpret_cast<uint64_t*>(Ws + (size_t)BN * p.w_stride);
     uint64_t* empty = full + MF_MAX_STAGES;
     uint64_t* rfull = empty + MF_MAX_STAGES;
-    uint64_t* rempty = rfull + 1;
-    uint64_t* tdone = rempty + 1;
+    uint64_t* rempty = rfull + 2;
+    uint64_t* tdone = rempty + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tdone + 1);
     volatile uint32_t& s_decision = *(tmem_slot + 1);
 
@@ -99,8 +103,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
 
     if (tid == 0) {
         for (int s = 0; s < MF_MAX_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        mbar_init(rfull, MF_COMPUTE / 32);
-        mbar_init(rempty, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&rfull[s], MF_COMPUTE / 32); mbar_init(&rempty[s], 1); }
         mbar_init(tdone, 1);
         mbar_fence_init();
     }
@@ -124,6 +127,16 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
             tma_load_2d(dst + bx * MF_BOX_BYTES, &maps.x[sg], ch * 128 + bx * 32, row0, &full[st], pol);
     };
 
+    // L2 prefetch of the boxes of a later item
+    auto prefetch = [&](int it) {
+        const int tl = it / p.n_chunks, ch = it % p.n_chunks;
+        const int T = (int)blockIdx.x + tl * G;
+        const int sg = T / p.tiles_per_seg, row0 = (T % p.tiles_per_seg) * 128;
+        int nb = (p.dk - ch * 128 + 31) / 32;
+        if (nb > 4) nb = 4;
+        for (int bx = 0; bx < nb; ++bx) tma_prefetch_2d(&maps.x[sg], ch * 128 + bx * 32, row0);
+    };
+
     uint32_t code = DEC_GO;
     if (warp == 0) {
         // ---------------- TMA producer; prefetches X while the parameters are still in flight
@@ -132,6 +145,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
         if (lane == 0) {
             const int pre = my_items < p.n_stages ? my_items : p.n_stages;
             for (; issued < pre; ++issued) issue(issued, pol);
+            for (int k = issued; k < issued + p.pf && k < my_items; ++k) prefetch(k);
             code = wait_for_parameters(p);
             s_decision = code;
         }
@@ -143,6 +157,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                 for (int k = 0; k < issued; ++k) mbar_wait(&full[k % p.n_stages], 0);
             } else {
                 for (int it = issued; it < my_items; ++it) {
+                    if (it + p.pf < my_items && p.pf > 0) prefetch(it + p.pf);
                     mbar_wait_backoff(&empty[it % p.n_stages], ((it / p.n_stages) - 1) & 1);
                     issue(it, pol);
                 }
@@ -155,11 +170,12 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
         if (code == DEC_GO && lane == 0) {
             // ---------------- backward MMA issuer
             constexpr uint32_t idesc = make_idesc_tf32(128, BN, /*a_mn_major=*/1, /*b_mn_major=*/0);
-            const uint32_t r_addr = smem_u32(Rs);
             int it = 0;
             for (int tl = 0; tl < my_tiles; ++tl) {
-                mbar_wait(rfull, tl & 1);
+                const int rb = tl % p.n_rbuf;
+                mbar_wait(&rfull[rb], (tl / p.n_rbuf) & 1);
                 tc_fence_after();
+                const uint32_t r_addr = smem_u32(Rs + rb * R_BYTES);
                 for (int ch = 0; ch < p.n_chunks; ++ch, ++it) {
                     const int st = it % p.n_stages;
                     mbar_wait(&full[st], (it / p.n_stages) & 1);
@@ -175,7 +191,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                     }
                     umma_commit(&empty[st]);          // slot reusable once these MMAs have read it
                 }
-                umma_commit(rempty);                  // R may be overwritten
+                umma_commit(&rempty[rb]);             // this R image may be overwritten
             }
             umma_commit(tdone);
         }
@@ -187,31 +203,31 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
             const int cw = warp - 4;                   // compute warp 0..7 owns tile rows cw*16 .. cw*16+15
             const int ct = tid - 128;                  // 0..255
             const int g = lane >> 2, t = lane & 3;
-            // ---------------- parameters -> shared memory as column pairs, tf32-rounded
-            for (int i = ct; i < (p.dk / 2) * BN; i += MF_COMPUTE) {
-                const int n = i % BN, cp = i / BN;
-                float2 w;
-                w.x = round_tf32(__ldcg(p.W + (size_t)n * p.ldw + 2 * cp));
-                w.y = round_tf32(__ldcg(p.W + (size_t)n * p.ldw + 2 * cp + 1));
-                *reinterpret_cast<float2*>(Ws + (size_t)cp * p.w_stride + 2 * n) = w;
+            // ---------------- parameters -> shared memory, class-major rows of dk + 4 floats, tf32-rounded
+            for (int i = ct; i < BN * p.dk; i += MF_COMPUTE) {
+                const int n = i / p.dk, c = i % p.dk;
+                Ws[(size_t)n * p.w_stride + c] = round_tf32(__ldcg(p.W + (size_t)n * p.ldw + c));
             }
             asm volatile("bar.sync 2, %0;" ::"r"(MF_COMPUTE) : "memory");
 
             // per-thread constants of the fragment addressing (shared-space byte addresses)
             const uint32_t ring_u = smem_u32(ring), ws_u = smem_u32(Ws), rs_u = smem_u32(Rs);
-            // X rows r0 = cw*16 + g and r0 + 8 (same r & 3): offset inside a box with the 32B-chunk XOR folded in
-            const int r0 = cw * 16 + g;
-            const uint32_t xoff = (uint32_t)r0 * 128u + (uint32_t)t * 8u + ((uint32_t)(r0 & 3) << 5);
-            const uint32_t woff = ws_u + (uint32_t)t * (uint32_t)p.w_stride * 4u + (uint32_t)g * 8u;
-            const uint32_t wstep = (uint32_t)p.w_stride * 16u;           // 4 column pairs = one k-step of 8 columns
+            // ldmatrix row addresses.  A: lane L -> tile row cw*16 + (L & 15), 16-byte half L >> 4 of the
+            // k-step's 32 bytes (the 32B-chunk XOR of the swizzle folded in).  B: lane L -> class
+            // (L & 7) + 8 * (L >> 4), 16-byte half (L >> 3) & 1; rows are dk*4 + 16 bytes apart (conflict-free).
+            const int ra = cw * 16 + (lane & 15);
+            const uint32_t xoff = (uint32_t)ra * 128u + ((uint32_t)(ra & 3) << 5) + (uint32_t)(lane >> 4) * 16u;
+            const uint32_t woff = ws_u + (uint32_t)((lane & 7) + 8 * (lane >> 4)) * (uint32_t)p.w_stride * 4u +
+                                  (uint32_t)((lane >> 3) & 1) * 16u;
+            const int r0 = cw * 16 + g;                // accumulator rows of this thread: r0 and r0 + 8
             // R^T image: sub-tile (32 rows) cw/2, row inside it rr = (cw&1)*16 + h*8 + g
             const int rr0 = (cw & 1) * 16 + g;
-            const uint32_t roff = rs_u + (uint32_t)(cw >> 1) * (BN * 128) + (uint32_t)(rr0 & 3) * 4u;
+            const uint32_t roff0 = rs_u + (uint32_t)(cw >> 1) * (BN * 128) + (uint32_t)(rr0 & 3) * 4u;
 
             int it = 0;
+            int sg = (int)blockIdx.x / p.tiles_per_seg, tis = (int)blockIdx.x % p.tiles_per_seg;
             for (int tl = 0; tl < my_tiles; ++tl) {
-                const int T = (int)blockIdx.x + tl * G;
-                const int sg = T / p.tiles_per_seg, row0 = (T % p.tiles_per_seg) * 128;
+                const int row0 = tis * 128;
                 const float cf = p.coeff[sg];
                 float yv[2];
                 bool valid[2];
@@ -234,28 +250,26 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                     const uint32_t stage = ring_u + (uint32_t)st * MF_STAGE_BYTES + xoff;
                     int nbx = (p.dk - ch * 128 + 31) / 32;
                     if (nbx > 4) nbx = 4;
-                    uint32_t wp = woff + (uint32_t)(ch * 16) * wstep;
+                    uint32_t wp = woff + (uint32_t)(ch * 128) * 4u;
 #pragma unroll
                     for (int bx = 0; bx < 4; ++bx) {
                         if (bx < nbx) {
-                            // logical k = t / t+4 of the instruction <-> physical columns 2t / 2t+1
-                            uint2 a[4][2], bfr[4][NBC];
+                            uint32_t a[4][4], bfr[4][NBC / 2][4];
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk) {
-                                const uint32_t xa = (stage + bx * MF_BOX_BYTES) ^ ((uint32_t)kk << 5);
-                                a[kk][0] = lds64(xa);
-                                a[kk][1] = lds64(xa + 8 * 128);
+                                ldsm_x4((stage + bx * MF_BOX_BYTES) ^ ((uint32_t)kk << 5), a[kk]);
 #pragma unroll
-                                for (int nb = 0; nb < NBC; ++nb) bfr[kk][nb] = lds64(wp + (uint32_t)kk * wstep + nb * 64);
+                                for (int np = 0; np < NBC / 2; ++np)      // two 8-class blocks per ldmatrix
+                                    ldsm_x4(wp + (uint32_t)kk * 32u + (uint32_t)np * 16u * (uint32_t)p.w_stride * 4u, bfr[kk][np]);
                             }
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
                                 for (int nb = 0; nb < NBC; ++nb)
-                                    mma_tf32_16x8x8(acc[nb], a[kk][0].x, a[kk][1].x, a[kk][0].y, a[kk][1].y, bfr[kk][nb].x,
-                                                    bfr[kk][nb].y);
+                                    mma_tf32_16x8x8(acc[nb], a[kk][0], a[kk][1], a[kk][2], a[kk][3], bfr[kk][nb >> 1][(nb & 1) * 2],
+                                                    bfr[kk][nb >> 1][(nb & 1) * 2 + 1]);
                         }
-                        wp += 4 * wstep;
+                        wp += 32 * 4;
                     }
                 }
 
@@ -306,7 +320,9 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                     }
                 }
                 // ---------------- R^T into the K-major SW128 operand image
-                if (tl > 0) mbar_wait(rempty, (tl - 1) & 1);
+                const int rb = tl % p.n_rbuf;
+                if (tl >= p.n_rbuf) mbar_wait(&rempty[rb], ((tl / p.n_rbuf) - 1) & 1);
+                const uint32_t roff = roff0 + (uint32_t)rb * R_BYTES;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int c16 = (rr0 + h * 8) >> 2;                   // 16-byte chunk of the row inside the sub-tile
@@ -320,7 +336,9 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) mbar_arrive(rfull);
+                if (lane == 0) mbar_arrive(&rfull[rb]);
+                tis += G;
+                while (tis >= p.tiles_per_seg) { tis -= p.tiles_per_seg; ++sg; }
             }
 
             // ---------------- accumulators: TMEM -> this CTA's partial [CN][ldw]
@@ -403,10 +421,9 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
 }
 
 // ------------------------------------------------------------------------------------ host
-static size_t mc_fused_smem(int dk, int BN, int stages) {
-    const size_t w_stride = 2 * BN + 16;
-    return 1024 + (size_t)stages * MF_STAGE_BYTES + (size_t)4 * BN * 128 + (size_t)(dk / 2) * w_stride * sizeof(float) +
-           (2 * MF_MAX_STAGES + 3) * sizeof(uint64_t) + 16;
+static size_t mc_fused_smem(int dk, int BN, int stages, int n_rbuf = 1) {
+    return 1024 + (size_t)stages * MF_STAGE_BYTES + (size_t)n_rbuf * 4 * BN * 128 + (size_t)BN * (dk + 4) * sizeof(float) +
+           (2 * MF_MAX_STAGES + 5) * sizeof(uint64_t) + 16;
 }
 
 // ring slots for this shape, 0 when the one-pass kernel cannot hold a whole tile
@@ -426,7 +443,7 @@ size_t mc_fused_scratch_bytes(int d, int CN) {
 
 template <int NBC>
 static int launch_fused(const McFusedMaps& maps, McFusedParams& p, int grid, cudaStream_t st) {
-    const size_t smem = mc_fused_smem(p.dk, 8 * NBC, p.n_stages);
+    const size_t smem = mc_fused_smem(p.dk, 8 * NBC, p.n_stages, p.n_rbuf);
     auto kern = mc_fused_kernel<NBC>;
     static bool attr_done = false;
     if (!attr_done) {
@@ -446,6 +463,8 @@ int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes,
     memset(&p, 0, sizeof(p));
     p.n_stages = mc_fused_stages(dk, CN);
     EH_REQUIRE(p.n_stages > 0, "grad_mc: one-pass kernel cannot hold %d columns", dk);
+    // a second R image (backward of tile t overlapping tile t+1) measured slower (0.69 vs 0.76 at d = 128): opt-in
+    p.n_rbuf = (mc_fused_smem(dk, CN, p.n_stages, 2) <= (size_t)227 * 1024 && getenv("EH_MC_RBUF2") != nullptr) ? 2 : 1;
     for (int sg = 0; sg < j->n_segs; ++sg) {
         EH_REQUIRE(j->d_X[sg] && j->d_y[sg], "grad_mc: null segment %d", sg);
         EH_REQUIRE(((uintptr_t)j->d_X[sg] % 16) == 0, "grad_mc: X must be 16-byte aligned");
@@ -459,7 +478,9 @@ int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes,
     p.W = j->d_W; p.out = j->d_out; p.flag = j->d_flag; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
     p.n_segs = j->n_segs; p.rows_per_seg = j->rows_per_seg; p.tiles_per_seg = (j->rows_per_seg + 127) / 128;
     p.d = j->d; p.dk = dk; p.ldw = j->ldw; p.n_chunks = (dk + 127) / 128; p.C = j->C; p.model = j->model;
-    p.w_stride = 2 * CN + 16;
+    p.w_stride = dk + 4;
+    // L2 prefetch two tiles ahead pays only when a tile spans two ring slots (d = 256: 0.84 -> 0.79 ms)
+    p.pf = (getenv("EH_MC_PF") ? atoi(getenv("EH_MC_PF")) : (p.n_chunks >= 2 ? 2 : 0)) * p.n_chunks;
     p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     const long long n_tiles = (long long)p.n_segs * p.tiles_per_seg;
