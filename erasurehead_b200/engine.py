@@ -95,6 +95,12 @@ class Engine:
         self.data = data
         self.first_round = 0
         self.on_gpu = self.ctx.device.type == "cuda"
+        if data is None and cfg.synthetic and not self.on_gpu:
+            # no GPU: --synthetic falls back to the host generator (generate_data.py distribution)
+            from .data import generate_gmm
+            task = {"linear": "linear", "softmax": "softmax"}.get(self.model.name, "logistic")
+            kw = dict(classes=self.model.n_out) if task == "softmax" else {}
+            self.data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=cfg.seed or 0, task=task, **kw)
         beta0 = oracle.initial_beta(self.spec, cfg.n_cols, cfg.seed, self.model.n_out)
         self.beta0 = self.ctx.broadcast_object(beta0 if self.ctx.is_root else None)
         self.u0 = np.zeros_like(self.beta0)
