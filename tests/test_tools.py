@@ -28,3 +28,23 @@ def test_makefile_targets_pass_13_positionals():
     assert p.returncode == 0
     for line in [l for l in p.stdout.splitlines() if "main.py" in l]:
         assert len(line.split("main.py")[1].split()) >= 13
+
+
+def test_command_map_covers_the_reference(monkeypatch, tmp_path):
+    """Every project-related entry of the reference's command map (pytorch_ec2.py:938-951) exists, and
+    the composite clean_launch_and_run runs its steps in the reference's order."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    ref = ["launch", "clean_launch_and_run", "shutdown", "get_hosts", "kill_all_python", "list_idle_instances",
+           "list_running_instances", "kill_python", "run_command", "setup_nfs"]
+    for name in ref:
+        p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "cluster.py"), name, "--help"],
+                           capture_output=True, text=True)
+        assert p.returncode == 0, (name, p.stderr)
+    calls = []
+    for fn in ("cmd_shutdown", "cmd_launch", "cmd_get_hosts", "cmd_bootstrap", "cmd_install", "cmd_torchrun"):
+        monkeypatch.setattr(cluster, fn, lambda a, _n=fn: calls.append(_n))
+    monkeypatch.setattr(cluster, "wait_until_running", lambda count, **kw: calls.append("wait"))
+    monkeypatch.chdir(tmp_path)
+    cluster.main(["clean_launch_and_run", "--count", "2", "--", "main.py", "9"])
+    assert calls == ["cmd_shutdown", "cmd_launch", "wait", "cmd_get_hosts", "cmd_bootstrap", "cmd_install", "cmd_torchrun"]

@@ -10,7 +10,14 @@ sense for GPU nodes:
   list_idle_instances <hostfile>               hosts with no GPU compute process (:304-336)
   kill_python <hostfile>                       stop the training processes this tool started (by recorded PID)
   setup_nfs <hostfile> <export_dir>            export a directory from the first host and mount it on the rest (:880-900)
-  install <hostfile>                           push SSH keys / build the CUDA library on every host (tools/*.sh role)
+  install <hostfile>                           build the CUDA library on every host (tools/install.sh role)
+  bootstrap <hostfile>                         node set-up of tools/local_script.sh / remote_script.sh: append the
+                                               `hosts` aliases to /etc/hosts, share one cluster SSH key pair, accept
+                                               host keys, so that every node reaches every other by alias
+  update_repo <hostfile>                       `git pull` in the repository on every host (tools/update_git_dir.sh role)
+  clean_launch_and_run --count N -- main.py <13 positionals>
+                                               shutdown, launch, wait until every instance is up and reachable,
+                                               get_hosts, bootstrap, install, torchrun (pytorch_ec2.py:938 map entry)
   torchrun --hostfile F --gpus-per-node G -- main.py <13 positionals>
                                                multi-node launch: one ``torch.distributed.run`` per host
 
@@ -95,6 +102,28 @@ def cmd_launch(a):
     print("launched", [i["InstanceId"] for i in r["Instances"]])
 
 
+def wait_until_running(count: int, timeout_s: int = 900, poll_s: int = 10):
+    """Block until `count` tagged instances are running and answer on port 22 (the reference's wait
+    loops, pytorch_ec2.py:209-256)."""
+    import socket
+    import time
+    t0 = time.time()
+    while time.time() - t0 < timeout_s:
+        inst = _instances()
+        if len(inst) >= count:
+            up = 0
+            for i in inst:
+                try:
+                    socket.create_connection((i.get("PublicIpAddress") or i["PrivateIpAddress"], 22), timeout=3).close()
+                    up += 1
+                except OSError:
+                    pass
+            if up >= count:
+                return inst
+        time.sleep(poll_s)
+    sys.exit(f"only {len(_instances())} of {count} instances came up within {timeout_s} s")
+
+
 def _instances(states=("running",)):
     ec2 = _ec2()
     r = ec2.describe_instances(Filters=[{"Name": "tag:Name", "Values": [cfg["name"]]},
@@ -156,6 +185,41 @@ def cmd_install(a):
     fan_out(read_hosts(a.hostfile), f"cd {repo} && bash csrc/build.sh | tail -1")
 
 
+def cmd_bootstrap(a):
+    """/etc/hosts aliases + one shared key pair + known_hosts on every node (tools/local_script.sh,
+    tools/remote_script.sh).  Reads the `hosts` file written by get_hosts from the current directory."""
+    hosts = read_hosts(a.hostfile)
+    lines = open("hosts").read().strip().replace("'", "") if os.path.exists("hosts") else ""
+    head = hosts[0]
+    # the head node creates the cluster key once; everyone authorises it and learns the aliases
+    fan_out([head], "test -f ~/.ssh/id_cluster || ssh-keygen -q -t ed25519 -N '' -f ~/.ssh/id_cluster; cat ~/.ssh/id_cluster.pub")
+    rc, pub, _ = ssh_run(head, "cat ~/.ssh/id_cluster.pub")
+    pub = pub.strip()
+    fan_out(hosts, f"mkdir -p ~/.ssh && chmod 700 ~/.ssh && grep -qF '{pub}' ~/.ssh/authorized_keys 2>/dev/null || "
+                   f"echo '{pub}' >> ~/.ssh/authorized_keys; "
+                   + (f"printf '%s\n' '{lines}' | while read ip al; do grep -q \"$al\" /etc/hosts || "
+                      f"echo \"$ip $al\" | sudo tee -a /etc/hosts >/dev/null; done; " if lines else "")
+                   + "for h in " + " ".join(hosts) + "; do ssh-keyscan -H $h >> ~/.ssh/known_hosts 2>/dev/null; done; true")
+
+
+def cmd_update_repo(a):
+    repo = a.repo or cfg["repo_dir"]
+    fan_out(read_hosts(a.hostfile), f"cd {repo} && git pull --ff-only | tail -1")
+
+
+def cmd_clean_launch_and_run(a):
+    """shutdown -> launch -> wait -> get_hosts -> bootstrap -> install -> torchrun."""
+    cmd_shutdown(a)
+    cmd_launch(a)
+    wait_until_running(a.count)
+    a.hostfile = None
+    cmd_get_hosts(a)
+    a.hostfile = "hosts_address"
+    cmd_bootstrap(a)
+    cmd_install(a)
+    cmd_torchrun(a)
+
+
 def cmd_torchrun(a):
     hosts = read_hosts(a.hostfile)
     master = hosts[0]
@@ -179,13 +243,17 @@ def main(argv=None):
     sub.add_parser("list_running_instances").set_defaults(fn=cmd_list_running)
     p = sub.add_parser("get_hosts"); p.add_argument("--hostfile"); p.set_defaults(fn=cmd_get_hosts)
     for name, fn in (("run_command", cmd_run_command), ("list_idle_instances", cmd_list_idle),
-                     ("kill_python", cmd_kill_python), ("kill_all_python", cmd_kill_python), ("install", cmd_install)):
+                     ("kill_python", cmd_kill_python), ("kill_all_python", cmd_kill_python), ("install", cmd_install),
+                     ("bootstrap", cmd_bootstrap), ("update_repo", cmd_update_repo)):
         p = sub.add_parser(name); p.add_argument("hostfile"); p.add_argument("--repo")
         p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=fn)
     p = sub.add_parser("setup_nfs"); p.add_argument("hostfile"); p.add_argument("export_dir"); p.set_defaults(fn=cmd_setup_nfs)
     p = sub.add_parser("torchrun"); p.add_argument("--hostfile", required=True)
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
     p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_torchrun)
+    p = sub.add_parser("clean_launch_and_run"); p.add_argument("--count", type=int, default=cfg["n_workers"])
+    p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
+    p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_clean_launch_and_run)
     a = ap.parse_args(argv)
     if getattr(a, "rest", None) and a.rest and a.rest[0] == "--":
         a.rest = a.rest[1:]
