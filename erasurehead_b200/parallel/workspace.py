@@ -22,6 +22,14 @@ from .context import DistContext
 class Workspace:
     def __init__(self, ctx: DistContext, n_workers: int, n_msgs: int, d: int):
         self.ctx = ctx
+        if ctx.world > 1:
+            import socket
+            hosts = ctx.all_gather_object(socket.gethostname())
+            if len(set(hosts)) > 1:
+                raise RuntimeError(
+                    "the peer-memory transport (CUDA IPC over NVLink/NVSwitch) needs every rank in one node; "
+                    f"ranks span {sorted(set(hosts))}.  Map the logical workers onto the GPUs of one node "
+                    "(n_procs - 1 workers are spread over the visible GPUs) or run one job per node.")
         L = lib()
         self.lay = WsLayout()
         check(L.eh_ws_layout_make(n_workers, n_msgs, d, C.byref(self.lay)), "eh_ws_layout_make")
