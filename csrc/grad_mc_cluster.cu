@@ -25,7 +25,7 @@
 
 #include "cluster_common.cuh"
 #include "grad_dense.cuh"
-#include "tc_common.cuh"
+#include "mc_common.cuh"
 
 namespace eh {
 
@@ -57,30 +57,6 @@ struct Mc2Params {
     uint32_t stamp, seq;
     unsigned long long timeout_ns;
 };
-
-__device__ __forceinline__ uint2 mc2_lds64(uint32_t addr) {
-    uint2 v;
-    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ float2 mc2_lds_f2(uint32_t addr) {
-    float2 v;
-    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ void mc2_sts32(uint32_t addr, float v) {
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
-}
-__device__ __forceinline__ void mc2_mma(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
-                                        uint32_t b1) {
-    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
-// residual of one margin given the row's label; softmax needs the row max / sum from the caller
-__device__ __forceinline__ float mc2_logistic(float margin, float y, float cf) {
-    return cf * __fdividef(-y, __expf(margin * y) + 1.0f);
-}
 
 template <int NBC>
 __global__ void __launch_bounds__(MC2_THREADS, 1)
@@ -241,7 +217,7 @@ mc_cluster_kernel(const __grid_constant__ Mc2Maps maps, const Mc2Params p) {
                     const float yv = valid ? __ldg(p.seg_y[sg] + grow) : 0.f;
                     float v0 = 0.f, v1 = 0.f;
                     for (int src = 0; src < CS * NPT; ++src) {
-                        const float2 t2 = mc2_lds_f2(xb_u + (uint32_t)slot * X_SLOT +
+                        const float2 t2 = mc_lds_f2(xb_u + (uint32_t)slot * X_SLOT +
                                                      (uint32_t)(((src * rows_own + row_local) * BN + 2 * cp) * 4));
                         v0 += t2.x; v1 += t2.y;
                     }
@@ -260,8 +236,8 @@ mc_cluster_kernel(const __grid_constant__ Mc2Maps maps, const Mc2Params p) {
                         r0v = cf * (e0 * inv - (n0 == yc ? 1.f : 0.f));
                         r1v = cf * (e1 * inv - (n0 + 1 == yc ? 1.f : 0.f));
                     } else {
-                        r0v = n0 < p.C ? mc2_logistic(v0, yv, cf) : 0.f;
-                        r1v = n0 + 1 < p.C ? mc2_logistic(v1, yv, cf) : 0.f;
+                        r0v = n0 < p.C ? mc_logistic(v0, yv, cf) : 0.f;
+                        r1v = n0 + 1 < p.C ? mc_logistic(v1, yv, cf) : 0.f;
                     }
                     r0v = valid ? round_tf32(r0v) : 0.f;
                     r1v = valid ? round_tf32(r1v) : 0.f;
@@ -334,16 +310,16 @@ mc_cluster_kernel(const __grid_constant__ Mc2Maps maps, const Mc2Params p) {
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk) {
                                 const uint32_t xa = (stage + bx * MC2_BOX) ^ ((uint32_t)kk << 5);
-                                a[kk][0] = mc2_lds64(xa);
-                                a[kk][1] = mc2_lds64(xa + 8 * 128);
+                                a[kk][0] = mc_lds64(xa);
+                                a[kk][1] = mc_lds64(xa + 8 * 128);
 #pragma unroll
-                                for (int nb = 0; nb < NBC; ++nb) bfr[kk][nb] = mc2_lds64(wp + (uint32_t)kk * wstep + nb * 64);
+                                for (int nb = 0; nb < NBC; ++nb) bfr[kk][nb] = mc_lds64(wp + (uint32_t)kk * wstep + nb * 64);
                             }
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
                                 for (int nb = 0; nb < NBC; ++nb)
-                                    mc2_mma(acc[nb], a[kk][0].x, a[kk][1].x, a[kk][0].y, a[kk][1].y, bfr[kk][nb].x, bfr[kk][nb].y);
+                                    mc_mma_tf32(acc[nb], a[kk][0].x, a[kk][1].x, a[kk][0].y, a[kk][1].y, bfr[kk][nb].x, bfr[kk][nb].y);
                         }
                         wp += 4 * wstep;
                     }
@@ -374,48 +350,15 @@ mc_cluster_kernel(const __grid_constant__ Mc2Maps maps, const Mc2Params p) {
                         const bool valid = grow < p.rows_per_seg;
                         const float yv = valid ? __ldg(p.seg_y[sg] + grow) : 0.f;
                         float res[NBC][2];
-                        if (p.model == 2) {
-                            float m = -3.0e38f;
-#pragma unroll
-                            for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                                for (int j = 0; j < 2; ++j)
-                                    if (nb * 8 + 2 * t + j < p.C) m = fmaxf(m, acc[nb][2 * h + j]);
-                            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-                            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-                            float sum = 0.f;
-#pragma unroll
-                            for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                                for (int j = 0; j < 2; ++j) {
-                                    const float e = (nb * 8 + 2 * t + j < p.C) ? __expf(acc[nb][2 * h + j] - m) : 0.f;
-                                    res[nb][j] = e;
-                                    sum += e;
-                                }
-                            sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                            sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-                            const float inv = __fdividef(1.f, sum);
-                            const int yc = (int)yv;
-#pragma unroll
-                            for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                                for (int j = 0; j < 2; ++j)
-                                    res[nb][j] = cf * (res[nb][j] * inv - ((nb * 8 + 2 * t + j) == yc ? 1.f : 0.f));
-                        } else {
-#pragma unroll
-                            for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                                for (int j = 0; j < 2; ++j)
-                                    res[nb][j] = (nb * 8 + 2 * t + j < p.C) ? mc2_logistic(acc[nb][2 * h + j], yv, cf) : 0.f;
-                        }
+                        mc_quad_row_residual<NBC>(acc, h, t, p.C, p.model, yv, cf, valid, res);
                         const uint32_t base = rs_u + (uint32_t)slot * R_SLOT + (uint32_t)(rt & 3) * 4u;
 #pragma unroll
                         for (int nb = 0; nb < NBC; ++nb)
 #pragma unroll
                             for (int j = 0; j < 2; ++j) {
                                 const int n = nb * 8 + 2 * t + j;
-                                mc2_sts32(base + (uint32_t)n * 128u + (uint32_t)(((rt >> 2) ^ (n & 7)) << 4),
-                                          valid ? round_tf32(res[nb][j]) : 0.f);
+                                mc_sts32(base + (uint32_t)n * 128u + (uint32_t)(((rt >> 2) ^ (n & 7)) << 4),
+                                          res[nb][j]);
                             }
                     }
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -25,7 +25,7 @@
 #include <stdlib.h>
 
 #include "grad_dense.cuh"
-#include "tc_common.cuh"
+#include "mc_common.cuh"
 
 namespace eh {
 
@@ -57,24 +57,6 @@ struct McFusedParams {
     uint32_t stamp, seq;
     unsigned long long timeout_ns;
 };
-
-// four 8x(16 byte) matrices: lane L supplies the row address of matrix L/8, row L%8; thread T gets the
-// 32-bit word T%4 of row T/4 of each matrix -- exactly the tf32 m16n8k8 fragment order
-__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-                 : "r"(addr));
-}
-__device__ __forceinline__ void sts32(uint32_t addr, float v) {
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
-}
-__device__ __forceinline__ void mma_tf32_16x8x8(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
-                                                uint32_t b0, uint32_t b1) {
-    asm(
-        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
 
 // NBC = 8-column blocks of the model (BN = 8 * NBC columns in the tensor-core tiles)
 template <int NBC>
@@ -257,16 +239,16 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                             uint32_t a[4][4], bfr[4][NBC / 2][4];
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk) {
-                                ldsm_x4((stage + bx * MF_BOX_BYTES) ^ ((uint32_t)kk << 5), a[kk]);
+                                mc_ldsm_x4((stage + bx * MF_BOX_BYTES) ^ ((uint32_t)kk << 5), a[kk]);
 #pragma unroll
                                 for (int np = 0; np < NBC / 2; ++np)      // two 8-class blocks per ldmatrix
-                                    ldsm_x4(wp + (uint32_t)kk * 32u + (uint32_t)np * 16u * (uint32_t)p.w_stride * 4u, bfr[kk][np]);
+                                    mc_ldsm_x4(wp + (uint32_t)kk * 32u + (uint32_t)np * 16u * (uint32_t)p.w_stride * 4u, bfr[kk][np]);
                             }
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk)
 #pragma unroll
                                 for (int nb = 0; nb < NBC; ++nb)
-                                    mma_tf32_16x8x8(acc[nb], a[kk][0], a[kk][1], a[kk][2], a[kk][3], bfr[kk][nb >> 1][(nb & 1) * 2],
+                                    mc_mma_tf32(acc[nb], a[kk][0], a[kk][1], a[kk][2], a[kk][3], bfr[kk][nb >> 1][(nb & 1) * 2],
                                                     bfr[kk][nb >> 1][(nb & 1) * 2 + 1]);
                         }
                         wp += 32 * 4;
@@ -276,49 +258,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                 // ---------------- residual per row (a row's columns live in the 4 lanes of a quad)
                 float res[2][NBC][2];
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    if (p.model == 2) {
-                        float m = -3.0e38f;
-#pragma unroll
-                        for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                            for (int j = 0; j < 2; ++j)
-                                if (nb * 8 + 2 * t + j < p.C) m = fmaxf(m, acc[nb][2 * h + j]);
-                        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-                        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-                        float sum = 0.f;
-#pragma unroll
-                        for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                            for (int j = 0; j < 2; ++j) {
-                                const float e = (nb * 8 + 2 * t + j < p.C) ? __expf(acc[nb][2 * h + j] - m) : 0.f;
-                                res[h][nb][j] = e;
-                                sum += e;
-                            }
-                        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-                        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
-                        const float inv = __fdividef(1.f, sum);
-                        const int yc = (int)yv[h];
-#pragma unroll
-                        for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                            for (int j = 0; j < 2; ++j) {
-                                const int n = nb * 8 + 2 * t + j;
-                                const float r = cf * (res[h][nb][j] * inv - (n == yc ? 1.f : 0.f));
-                                res[h][nb][j] = valid[h] ? round_tf32(r) : 0.f;
-                            }
-                    } else {
-#pragma unroll
-                        for (int nb = 0; nb < NBC; ++nb)
-#pragma unroll
-                            for (int j = 0; j < 2; ++j) {
-                                const int n = nb * 8 + 2 * t + j;
-                                const float z = acc[nb][2 * h + j] * yv[h];
-                                const float r = cf * __fdividef(-yv[h], __expf(z) + 1.0f);
-                                res[h][nb][j] = (valid[h] && n < p.C) ? round_tf32(r) : 0.f;
-                            }
-                    }
-                }
+                for (int h = 0; h < 2; ++h) mc_quad_row_residual<NBC>(acc, h, t, p.C, p.model, yv[h], cf, valid[h], res[h]);
                 // ---------------- R^T into the K-major SW128 operand image
                 const int rb = tl % p.n_rbuf;
                 if (tl >= p.n_rbuf) mbar_wait(&rempty[rb], ((tl / p.n_rbuf) - 1) & 1);
@@ -331,7 +271,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
 #pragma unroll
                         for (int j = 0; j < 2; ++j) {
                             const int n = nb * 8 + 2 * t + j;
-                            sts32(roff + (uint32_t)n * 128u + (uint32_t)((c16 ^ (n & 7)) << 4), res[h][nb][j]);
+                            mc_sts32(roff + (uint32_t)n * 128u + (uint32_t)((c16 ^ (n & 7)) << 4), res[h][nb][j]);
                         }
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
