@@ -8,6 +8,11 @@ set -e
 HERE="$(cd "$(dirname "$0")" && pwd)"
 SRC="${1:-/root/reference}"
 DST="$HERE/_ref_py3"
+if [ ! -f "$SRC/main.py" ]; then
+  # e.g. on a GPU box, where only the repository travels: keep an existing patched copy
+  [ -f "$DST/main.py" ] && { echo "no reference at $SRC; keeping $DST"; exit 0; }
+  echo "no reference at $SRC and no patched copy at $DST" >&2; exit 1
+fi
 rm -rf "$DST"; mkdir -p "$DST"
 cp -r "$SRC/main.py" "$SRC/src" "$DST/"
 cd "$DST"
