@@ -150,7 +150,13 @@ int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_byte
  * W[CN][ldw] (CN = 16 for C <= 16, else 32; ldw = d padded to 32) so a C-column model is one flat
  * vector of CN*ldw floats for the decoder.  d_out (may be peer memory) receives the encoded
  * gradient, d_loss (optional, zeroed by the caller) the summed loss.  No counterpart in the
- * reference (single-vector models only); BASELINE.json config "Covertype-shaped multi-class". */
+ * reference (single-vector models only); BASELINE.json config "Covertype-shaped multi-class".
+ *
+ * Kernel selection for a gradient call (d_out set, d_loss NULL): d <= 256 -> one pass, one launch
+ * (warp-level MMA forward + tcgen05 backward from one shared-memory tile, grad_mc_fused.cu);
+ * d <= 1024 -> the same on thread-block clusters (grad_mc_cluster.cu); wider, or with d_loss ->
+ * two tcgen05 passes (grad_mc_tc.cu).  The scratch buffer must be zero-filled when it is
+ * allocated (the one-pass kernels keep their barrier words in it and leave them zero). */
 typedef struct eh_mc_job {
     const float*    d_X[EH_MAX_SEGS];
     const float*    d_y[EH_MAX_SEGS];
