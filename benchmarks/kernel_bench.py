@@ -159,6 +159,8 @@ def bench_mc(args, pk, src):
         shapes = tuple(tuple(int(v) for v in sh.split(",")) for sh in args.mc_shapes)
     for rows, d, C_ in shapes:
         X, _ = synth.synth_gmm(rows, d, 1, 0)
+        if args.mc_bf16:
+            X = X.to(torch.bfloat16)
         y = torch.randint(0, C_, (rows,), device="cuda").float()
         Wp = mc.pack_params(torch.randn(d, C_, device="cuda") * 0.01)
         G = torch.empty_like(Wp)
@@ -166,15 +168,17 @@ def bench_mc(args, pk, src):
         job = mc.make_job([X], [y], Wp.data_ptr(), G.data_ptr(), d, C_, [1.0], mc.MODEL_SOFTMAX)
         med, mn = time_fn(lambda: mc.launch(job, scr), args.iters)
         one_pass = os.environ.get("EH_MC_TWOPASS") is None and (d <= 1024 or (d <= 4096 and os.environ.get("EH_MC_ONEPASS") == "cluster"))
-        Xd = X[:, :d]
+        Xd = X[:, :d].float() if args.mc_bf16 else X[:, :d]
         W = torch.randn(d, C_, device="cuda") * 0.01
         def torch_ref():
             S = torch.softmax(Xd @ W, 1)
             S[torch.arange(rows, device="cuda"), y.long()] -= 1
             return Xd.t() @ S
         med2, _ = time_fn(torch_ref, max(3, args.iters // 2))
-        byt = rows * X.stride(0) * 4
-        rec = {"kernel": "grad_mc(one pass: mma.sync fwd + tcgen05 bwd, %s)" % os.environ.get("EH_MC_ONEPASS", "auto") if one_pass else "grad_mc(tcgen05 fwd+bwd, softmax)",
+        byt = rows * X.stride(0) * (2 if args.mc_bf16 else 4)
+        if args.mc_bf16:
+            one_pass = True
+        rec = {"kernel": "grad_mc(bf16 rows: tcgen05 fwd + tcgen05 bwd, one tile)" if args.mc_bf16 else "grad_mc(one pass: mma.sync fwd + tcgen05 bwd, %s)" % os.environ.get("EH_MC_ONEPASS", "auto") if one_pass else "grad_mc(tcgen05 fwd+bwd, softmax)",
                "rows": rows, "d": d, "C": C_, "ms": med, "ms_min": mn, "cs_forced": os.environ.get("EH_MC_CS"),
                "X_passes": 1 if one_pass else 2, "GBps_algorithmic(1 pass)": byt / med / 1e6,
                "frac_of_hbm_" + src + "_one_pass_roofline": byt / med / 1e6 / pk["hbm_gbs"],
@@ -190,6 +194,7 @@ if __name__ == "__main__":
     ap.add_argument("--cols", type=int, nargs="+", default=[4096, 1024, 2048, 8192, 512])
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--only", default="")
+    ap.add_argument("--mc-bf16", action="store_true", help="bf16 feature rows for --only mc")
     ap.add_argument("--mc-shapes", nargs="*", default=[], help="rows,d,C triples for --only mc")
     ap.add_argument("--out", default="")
     args = ap.parse_args()

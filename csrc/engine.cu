@@ -38,7 +38,7 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
             const float* beta = plan->d_beta_local ? plan->d_beta_local + (size_t)par * lay.d_pad
                                                    : ws_beta(plan->d_ws_local, lay, par);
             int rc = EH_OK;
-            if (wj.sparse == 2) {
+            if (wj.sparse == 2 || wj.sparse == 4) {
                 rc = flush();
                 if (rc) return rc;
                 eh_mc_job j;
@@ -52,6 +52,7 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.ld = wj.ld_or_nnz;
                 j.ldw = (wj.d + 31) / 32 * 32; j.C = wj.classes; j.model = wj.model; j.stamp = stamp;
                 j.timeout_ns = plan->timeout_ns;
+                j.x_bf16 = (wj.sparse == 4);
                 rc = eh_grad_mc(&j, plan->d_scratch, plan->scratch_bytes, stream);
             } else if (!wj.sparse || wj.sparse == 3) {
                 eh_grad_job j;

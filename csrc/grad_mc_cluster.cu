@@ -171,19 +171,17 @@ mc_cluster_kernel(const __grid_constant__ Mc2Maps maps, const Mc2Params p) {
                 mbar_wait(&rfull[slot], (tl >> 2) & 1);
                 if (!direct) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 tc_fence_after();
-                const uint32_t r_addr = smem_u32(Rs + slot * R_SLOT);
+                const uint64_t r_desc = make_kmajor_sw128_desc(smem_u32(Rs + slot * R_SLOT));
                 for (int ch = 0; ch < mych; ++ch, ++it) {
                     const int st = it % p.n_stages;
                     mbar_wait(&full[st], (it / p.n_stages) & 1);
                     tc_fence_after();
-                    const uint32_t a_addr = smem_u32(ring + (size_t)st * MC2_STAGE);
+                    const uint64_t a_desc0 = make_mnmajor_sw128_32b_desc(smem_u32(ring + (size_t)st * MC2_STAGE), MC2_BOX);
                     const uint32_t d_tmem = tmem_base + ch * BN;
 #pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        const uint64_t a_desc = make_mnmajor_sw128_32b_desc(a_addr + kk * 1024, MC2_BOX);
-                        const uint64_t b_desc = make_kmajor_sw128_desc(r_addr) + (uint64_t)(kk * 2);
-                        umma_tf32(d_tmem, a_desc, b_desc, idesc, (tl > 0 || kk > 0) ? 1u : 0u);
-                    }
+                    for (int kk = 0; kk < 4; ++kk)
+                        umma_tf32(d_tmem, a_desc0 + (uint64_t)(kk * (1024 >> 4)), r_desc + (uint64_t)(kk * 2), idesc,
+                                  (tl > 0 || kk > 0) ? 1u : 0u);
                     umma_commit(&empty[st]);
                 }
                 umma_commit(&rempty[slot]);

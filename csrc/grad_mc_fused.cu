@@ -157,20 +157,21 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
                 const int rb = tl % p.n_rbuf;
                 mbar_wait(&rfull[rb], (tl / p.n_rbuf) & 1);
                 tc_fence_after();
-                const uint32_t r_addr = smem_u32(Rs + rb * R_BYTES);
+                // descriptors differ only in their 14-bit start-address field: build one, then add (the
+                // issuing thread is a single instruction stream -- every saved instruction is MMA rate)
+                const uint64_t r_desc = make_kmajor_sw128_desc(smem_u32(Rs + rb * R_BYTES));
                 for (int ch = 0; ch < p.n_chunks; ++ch, ++it) {
                     const int st = it % p.n_stages;
                     mbar_wait(&full[st], (it / p.n_stages) & 1);
                     tc_fence_after();
-                    const uint32_t a_addr = smem_u32(ring + (size_t)st * MF_STAGE_BYTES);
+                    // A: X^T, MN-major; 8 rows per MMA = 1024 B, 32-column atoms one box apart
+                    const uint64_t a_desc0 = make_mnmajor_sw128_32b_desc(smem_u32(ring + (size_t)st * MF_STAGE_BYTES), MF_BOX_BYTES);
                     const uint32_t d_tmem = tmem_base + ch * BN;
 #pragma unroll
-                    for (int kk = 0; kk < 16; ++kk) {
-                        // A: X^T, MN-major; 8 rows per MMA = 1024 B, 32-column atoms one box apart
-                        const uint64_t a_desc = make_mnmajor_sw128_32b_desc(a_addr + kk * 1024, MF_BOX_BYTES);
-                        const uint64_t b_desc = make_kmajor_sw128_desc(r_addr + (kk >> 2) * (BN * 128)) + (uint64_t)((kk & 3) * 2);
-                        umma_tf32(d_tmem, a_desc, b_desc, idesc, (tl > 0 || kk > 0) ? 1u : 0u);
-                    }
+                    for (int kk = 0; kk < 16; ++kk)
+                        umma_tf32(d_tmem, a_desc0 + (uint64_t)(kk * (1024 >> 4)),
+                                  r_desc + (uint64_t)((kk >> 2) * ((BN * 128) >> 4) + (kk & 3) * 2), idesc,
+                                  (tl > 0 || kk > 0) ? 1u : 0u);
                     umma_commit(&empty[st]);          // slot reusable once these MMAs have read it
                 }
                 umma_commit(&rempty[rb]);             // this R image may be overwritten

@@ -354,6 +354,9 @@ static int launch_bwd(const CUtensorMap& mx, const CUtensorMap& mr, const McBwdP
 int mc_fused_stages(int dk, int CN);
 size_t mc_fused_scratch_bytes(int d, int CN);
 int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
+// bf16 rows, both products on tcgen05 (grad_mc_bf16.cu)
+int mc_bf16_stages(int dk, int CN);
+int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
 // one-pass kernel on thread-block clusters (grad_mc_cluster.cu)
 bool mc_cluster_plan(int dk, int CN, int* cs_out, int* npc_out, int* stages_out);
 int mc_cluster_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
@@ -372,7 +375,8 @@ extern "C" size_t eh_grad_mc_scratch_bytes(int64_t rows_per_seg, int d, int C) {
     const int CN = C <= 16 ? 16 : 32;
     size_t b = eh::mc_twopass_scratch_bytes(rows_per_seg, d, CN);
     const int dk = (d + 31) / 32 * 32;
-    if (eh::mc_fused_stages(dk, CN) > 0 || eh::mc_cluster_plan(dk, CN, nullptr, nullptr, nullptr))
+    if (eh::mc_fused_stages(dk, CN) > 0 || eh::mc_cluster_plan(dk, CN, nullptr, nullptr, nullptr) ||
+        eh::mc_bf16_stages(dk, CN) > 0)
         b += eh::mc_fused_scratch_bytes(d, CN);
     return b;
 }
@@ -393,6 +397,11 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
                "grad_mc: d * classes exceeds one CTA's tensor memory (%d chunks x %d columns > 512)", n_chunks, CN);
     EH_REQUIRE(scratch_bytes >= eh_grad_mc_scratch_bytes(j->rows_per_seg, j->d, j->C), "grad_mc: scratch too small");
     cudaStream_t st = (cudaStream_t)stream;
+    if (j->x_bf16) {
+        EH_REQUIRE(j->d_out && !j->d_loss, "grad_mc: bf16 rows are supported for the gradient call only");
+        const size_t off = mc_twopass_scratch_bytes(j->rows_per_seg, j->d, CN);
+        return mc_bf16_launch(j, (char*)d_scratch + off, scratch_bytes - off, st);
+    }
     // gradient of a narrow model: one pass over X, one launch (grad_mc_fused.cu)
     if (j->d_out && !j->d_loss && getenv("EH_MC_TWOPASS") == nullptr) {
         const size_t off = mc_twopass_scratch_bytes(j->rows_per_seg, j->d, CN);

@@ -137,7 +137,10 @@ class Engine:
         mine = ctx.local_workers(spec.n)
         needed = sorted({sg.partition for w in mine for sg in spec.segments[w]})
         self.sparse = bool(self.data.is_sparse) if self.data is not None else False
-        self.bf16 = cfg.dtype == "bf16" and not self.sparse and not self.mc
+        self.bf16 = cfg.dtype == "bf16" and not self.sparse
+        if self.bf16 and self.mc and _pad32(cfg.n_cols) > 640:
+            raise ValueError("--dtype=bf16 with a multi-column model needs n_cols <= 640 "
+                             "(one-pass tensor-core kernel); use fp32 features for wider models")
         if cfg.dtype not in ("fp32", "bf16"):
             raise ValueError("dtype must be fp32 or bf16")
         for p in needed:
@@ -155,7 +158,7 @@ class Engine:
                             f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
                             "use fewer partitions per worker")
                 j = _lib.WorkerJob()
-                jkind = 2 if self.mc else (1 if self.sparse else (3 if self.bf16 else 0))
+                jkind = (4 if self.bf16 else 2) if self.mc else (1 if self.sparse else (3 if self.bf16 else 0))
                 j.worker, j.msg, j.sparse, j.model = w, kind, jkind, self.model.device_id
                 j.classes = self.model.n_out
                 j.n_segs, j.rows_per_seg, j.d = len(segs), spec.rows_per_part, d
@@ -497,6 +500,8 @@ class Engine:
             tot, rows = 0.0, 0
             for p in range(n_parts):
                 Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
+                if Xp.dtype != torch.float32:
+                    Xp = Xp.float()                  # the loss-only kernels read fp32 rows
                 tot += float(mc.loss_mc(Xp, yp, Wp, d, C_, self.model.device_id).item())
                 rows += Xp.shape[0]
             tr[i] = tot / rows

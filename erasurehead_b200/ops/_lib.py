@@ -72,7 +72,7 @@ class McJob(C.Structure):
                 ("d_beta_flag", C.c_void_p), ("d_err", C.c_void_p),
                 ("n_segs", C.c_int32), ("rows_per_seg", C.c_int32), ("d", C.c_int32), ("ld", C.c_int32),
                 ("ldw", C.c_int32), ("C", C.c_int32), ("model", C.c_int32), ("stamp", C.c_uint32),
-                ("timeout_ns", C.c_uint64)]
+                ("timeout_ns", C.c_uint64), ("x_bf16", C.c_int32), ("reserved", C.c_int32)]
 
 
 class DecoderDesc(C.Structure):

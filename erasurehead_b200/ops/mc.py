@@ -51,8 +51,10 @@ def make_job(Xs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], W_ptr: int,
              beta_flag_ptr: int = 0, err_ptr: int = 0, timeout_ns: int = 0) -> McJob:
     job = McJob()
     X0 = Xs[0]
+    bf16 = X0.dtype == torch.bfloat16          # bf16 rows: all-tcgen05 one-pass kernel (csrc/grad_mc_bf16.cu)
     for i, (X, y) in enumerate(zip(Xs, ys)):
-        assert X.dtype == torch.float32 and X.stride(1) == 1 and X.stride(0) == X0.stride(0) and X.shape[0] == X0.shape[0]
+        assert X.dtype == X0.dtype and X.dtype in (torch.float32, torch.bfloat16)
+        assert X.stride(1) == 1 and X.stride(0) == X0.stride(0) and X.shape[0] == X0.shape[0]
         assert y.dtype == torch.float32 and y.is_contiguous()
         job.d_X[i], job.d_y[i], job.coeff[i] = X.data_ptr(), y.data_ptr(), float(coeff[i])
     job.n_segs, job.rows_per_seg = len(Xs), X0.shape[0]
@@ -60,6 +62,7 @@ def make_job(Xs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], W_ptr: int,
     job.d_W, job.d_out, job.d_loss = W_ptr, out_ptr, loss_ptr
     job.d_flag, job.d_beta_flag, job.d_err = flag_ptr, beta_flag_ptr, err_ptr
     job.stamp, job.timeout_ns = int(stamp), int(timeout_ns)
+    job.x_bf16 = 1 if bf16 else 0
     return job
 
 

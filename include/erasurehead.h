@@ -155,7 +155,8 @@ int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_byte
  * Kernel selection for a gradient call (d_out set, d_loss NULL): d <= 256 -> one pass, one launch
  * (warp-level MMA forward + tcgen05 backward from one shared-memory tile, grad_mc_fused.cu);
  * d <= 1024 -> the same on thread-block clusters (grad_mc_cluster.cu); wider, or with d_loss ->
- * two tcgen05 passes (grad_mc_tc.cu).  The scratch buffer must be zero-filled when it is
+ * two tcgen05 passes (grad_mc_tc.cu).  bf16 feature rows (x_bf16, d <= 640): both products on
+ * tcgen05 from one shared-memory tile (grad_mc_bf16.cu).  The scratch buffer must be zero-filled when it is
  * allocated (the one-pass kernels keep their barrier words in it and leave them zero). */
 typedef struct eh_mc_job {
     const float*    d_X[EH_MAX_SEGS];
@@ -172,6 +173,8 @@ typedef struct eh_mc_job {
     int32_t         model;
     uint32_t        stamp;
     uint64_t        timeout_ns;
+    int32_t         x_bf16;         /* d_X are bf16 rows (ld in elements, ld % 8 == 0): all-tcgen05 one-pass kernel, d <= 640 */
+    int32_t         reserved;
 } eh_mc_job;
 
 size_t eh_grad_mc_scratch_bytes(int64_t rows_per_seg, int d, int C);
@@ -236,7 +239,8 @@ int eh_decoder_publish(const eh_decoder_desc* desc, int round, void* stream);
 typedef struct eh_worker_job {
     int32_t  worker;                 /* global worker id (slot row on the root) */
     int32_t  msg;                    /* EH_MSG_CODED / EH_MSG_PRIVATE */
-    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL, 2: dense multi-column (tensor cores), 3: dense bf16 rows */
+    int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL, 2: dense multi-column (tensor cores), 3: dense bf16 rows,
+                                        4: dense multi-column with bf16 rows (d <= 640) */
     int32_t  model;
     int32_t  n_segs, rows_per_seg;
     int32_t  d, ld_or_nnz;           /* dense: row stride; ELL: ones per row */

@@ -174,6 +174,26 @@ def test_engine_softmax_multiclass_matches_oracle():
     eng2.close()
 
 
+def test_engine_softmax_bf16_rows_matches_oracle_on_rounded_data():
+    """--dtype=bf16 with a multi-class model: the all-tcgen05 one-pass kernel (csrc/grad_mc_bf16.cu)."""
+    import torch
+    C_ = 6
+    cfg = mk("approx", s=1, k=6, rows=8 * 512, d=200, model="softmax", classes=C_, eta0=0.5, rounds=5, dtype="bf16")
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 8, seed=1, task="softmax", classes=C_)
+    data.parts = [torch.from_numpy(p).to(torch.bfloat16).double().numpy() for p in data.parts]
+    dl = spaced_delays(cfg.rounds, 8, seed=4)
+    eng = Engine(cfg, data, delays=dl)
+    assert eng.bf16 and eng.mc and eng.parts[0][0].dtype == torch.bfloat16
+    res = eng.run()
+    ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl, beta0=eng.beta0, model=eng.model)
+    scale = max(1.0, np.abs(ref.betaset).max())
+    assert np.abs(res.betaset - ref.betaset).max() <= 2e-2 * scale        # W and the residual are bf16 MMA operands
+    assert np.array_equal(res.n_collected, ref.n_collected)
+    ev = eng.evaluate(res)
+    assert ev.training_loss[-1] < ev.training_loss[0]
+    eng.close()
+
+
 def test_debug_poison_mode_runs_clean():
     """NaN-poisoned slots: a correct run never reads a slot nobody wrote (sanitizer substitute)."""
     cfg = mk("approx", s=1, k=5, debug_poison=True)

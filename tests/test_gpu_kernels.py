@@ -250,6 +250,46 @@ def test_grad_mc_one_pass_kernels(rows, d, C, model, variant, monkeypatch):
     assert (mc.unpack_params(G3, d, C).double() - got).abs().max().item() <= 4e-3 * scale
 
 
+@pytest.mark.parametrize("rows,d,C,model", [(256, 128, 4, 2), (1000, 200, 7, 2), (777, 96, 20, 2), (1500, 54, 7, 2),
+                                            (90000, 256, 16, 2), (70001, 120, 5, 3), (30000, 512, 10, 2),
+                                            (5000, 640, 3, 3)])
+def test_grad_mc_bf16_rows_all_tcgen05(rows, d, C, model):
+    """bf16 feature rows: forward (K-major) and backward (MN-major) tcgen05 products from the same
+    128B-swizzled TMA tile, one launch.  Reference: fp64 torch on the same bf16 values; W and the
+    residual are rounded to bf16 as MMA operands, hence the looser tolerance."""
+    from erasurehead_b200.ops import mc, synth
+    torch.manual_seed(rows + d + C)
+    ld = synth.pad_cols(d)
+    Xs, ys = [], []
+    for _ in range(2):
+        X = torch.zeros(rows, ld, device=DEV, dtype=torch.bfloat16)
+        X[:, :d] = (torch.randn(rows, d, device=DEV) / np.sqrt(d)).to(torch.bfloat16)
+        Xs.append(X)
+        ys.append(torch.randint(0, C, (rows,), device=DEV).float() if model == 2
+                  else torch.where(torch.rand(rows, device=DEV) > 0.5, 1.0, -1.0))
+    W = torch.randn(d, C, device=DEV)
+    Wp = mc.pack_params(W)
+    cf = [1.0, -0.6]
+    G, _ = mc.grad_mc(Xs, ys, Wp, d, C, coeff=cf, model=model)
+    G2, _ = mc.grad_mc(Xs, ys, Wp, d, C, coeff=cf, model=model)
+    assert torch.equal(G, G2)
+    want = torch.zeros(d, C, dtype=torch.float64, device=DEV)
+    Wb = W.to(torch.bfloat16).double()
+    for X, y, c in zip(Xs, ys, cf):
+        P = X[:, :d].double() @ Wb
+        if model == 2:
+            R = torch.softmax(P, dim=1)
+            R[torch.arange(rows), y.long()] -= 1.0
+        else:
+            yy = y.double()[:, None]
+            R = -yy / (torch.exp(P * yy) + 1)
+        want += X[:, :d].double().t() @ (c * R)
+    got = mc.unpack_params(G, d, C).double()
+    scale = max(1.0, want.abs().max().item())
+    assert (got - want).abs().max().item() <= 1.5e-2 * scale
+    assert torch.all(G[C:] == 0) and torch.all(G[:, d:] == 0)
+
+
 @pytest.mark.parametrize("d", [96, 1024, 3000])
 def test_grad_dense_multi_batches_messages_in_one_launch(d):
     """Several messages (different partition counts / coefficients) share one launch."""
