@@ -45,9 +45,11 @@ def ell(rows, d, nnz, reps=2):
     assert torch.isfinite(o).all()
 
 
-def mc_fused(rows, d, C_, reps=2):
+def mc_fused(rows, d, C_, reps=2, bf16=False):
     from erasurehead_b200.ops import mc, synth
     X, _ = synth.synth_gmm(rows, d, 1, 0)
+    if bf16:
+        X = X.to(torch.bfloat16)
     y = torch.randint(0, C_, (rows,), device="cuda").float()
     Wp = mc.pack_params(torch.randn(d, C_, device="cuda") * 0.01)
     G = torch.empty_like(Wp)
@@ -88,6 +90,8 @@ if __name__ == "__main__":
             mc_fused(2097152, 128, 10)
         elif w == "mc_fused256":
             mc_fused(1048576, 256, 16)
+        elif w == "mc_bf16":
+            mc_fused(4194304, 256, 16, bf16=True)
         elif w == "mc_cluster":
             mc_fused(524288, 1024, 16)
         elif w == "round":
