@@ -8,7 +8,7 @@ import pytest
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ALL = ["naive", "coded", "replication", "avoidstragg", "approx", "partial_coded", "partial_replication", "sparse",
-       "softmax"]
+       "softmax", "softmax_bf16"]
 
 
 def _free_port():
