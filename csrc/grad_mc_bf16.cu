@@ -22,8 +22,10 @@
 //            as bf16 into the K-major SW128 operand image, fence.proxy.async, arrive
 //   tail     TMEM -> per-CTA partial, device-wide barrier, fixed-order reduction, ship + flag
 //
-// Parameters / messages stay fp32 ([CN][ldw], as for the other multi-column kernels); W and R are
-// rounded to bf16 only as MMA operands, accumulation is fp32.  dk <= 640.
+// Parameters / messages stay fp32 ([CN][ldw], as for the other multi-column kernels).  For up to 16
+// model columns W and R enter the MMAs as hi + lo bf16 pairs (twice the tile columns, halves added
+// after the products), so only the stored features carry bf16 precision; wider models round W and R
+// to bf16.  Accumulation is fp32.  dk <= 640.
 // No counterpart in the reference (single-vector fp64 models, naive.py:137-139).
 #include <cuda_bf16.h>
 #include <stdlib.h>
@@ -87,10 +89,14 @@ __device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr, 
 }
 __device__ __forceinline__ unsigned short bf16_bits(float v) { return __bfloat16_as_ushort(__float2bfloat16_rn(v)); }
 
-template <int NB>                       // BN = 16 * NB classes in the tensor-core tiles
+// BN = 16 * NB columns in the tensor-core tiles.  SPLIT: the fp32 parameters and residuals enter the MMAs as
+// hi + lo bf16 pairs (columns c and c + BN/2), i.e. with 16 mantissa bits, and the two halves are added
+// after the products -- only the stored features are bf16, as in the single-column bf16 kernel.
+template <int NB, bool SPLIT>
 __global__ void __launch_bounds__(MB_THREADS, 1)
 mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
     constexpr int BN = 16 * NB;
+    constexpr int CO = SPLIT ? BN / 2 : BN;           // model columns (rows of the output)
     constexpr int R_BYTES = 2 * BN * 128;             // two K-major sub-tiles [BN x 64 rows] bf16
     constexpr int W_BOX = BN * 128;                   // [BN x 64 columns] bf16
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -243,12 +249,18 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
             const int eg = (warp - 4) >> 2;            // epilogue group: tiles tl = eg, eg + MB_GROUPS, ...
             const int et = tid - 128;
             // ---------------- W^T as bf16 into the K-major SW128 operand image, one box per 64 columns
-            for (int i = et; i < BN * p.n_chunks * 128; i += MB_GROUPS * 128) {
+            for (int i = et; i < CO * p.n_chunks * 128; i += MB_GROUPS * 128) {
                 const int n = i / (p.n_chunks * 128), c = i % (p.n_chunks * 128);
                 const float w = (c < p.ldw) ? __ldcg(p.W + (size_t)n * p.ldw + c) : 0.f;
                 const int box = c >> 6, cc = c & 63;
-                *reinterpret_cast<unsigned short*>(Ws + (size_t)box * W_BOX + n * 128 + (((cc >> 3) ^ (n & 7)) << 4) + (cc & 7) * 2) =
-                    bf16_bits(w);
+                unsigned char* at = Ws + (size_t)box * W_BOX + (cc & 7) * 2;
+                const unsigned short hi = bf16_bits(w);
+                *reinterpret_cast<unsigned short*>(at + n * 128 + (((cc >> 3) ^ (n & 7)) << 4)) = hi;
+                if constexpr (SPLIT) {
+                    const int n2 = n + CO;
+                    *reinterpret_cast<unsigned short*>(at + n2 * 128 + (((cc >> 3) ^ (n2 & 7)) << 4)) =
+                        bf16_bits(w - __uint_as_float((uint32_t)hi << 16));
+                }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
@@ -277,23 +289,27 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tempty[as]);
+                if constexpr (SPLIT) {
+#pragma unroll
+                    for (int c = 0; c < CO; ++c) v[c] += v[c + CO];
+                }
                 if (p.model == 2) {
                     float m = -3.0e38f;
 #pragma unroll
-                    for (int c = 0; c < BN; ++c) if (c < p.C) m = fmaxf(m, v[c]);
+                    for (int c = 0; c < CO; ++c) if (c < p.C) m = fmaxf(m, v[c]);
                     float s = 0.f;
 #pragma unroll
-                    for (int c = 0; c < BN; ++c) {
+                    for (int c = 0; c < CO; ++c) {
                         v[c] = (c < p.C) ? __expf(v[c] - m) : 0.f;
                         s += v[c];
                     }
                     const float inv = __fdividef(1.f, s);
                     const int yc = (int)yv;
 #pragma unroll
-                    for (int c = 0; c < BN; ++c) v[c] = valid ? cf * (v[c] * inv - (c == yc ? 1.f : 0.f)) : 0.f;
+                    for (int c = 0; c < CO; ++c) v[c] = valid ? cf * (v[c] * inv - (c == yc ? 1.f : 0.f)) : 0.f;
                 } else {
 #pragma unroll
-                    for (int c = 0; c < BN; ++c)
+                    for (int c = 0; c < CO; ++c)
                         v[c] = (valid && c < p.C) ? cf * __fdividef(-yv, __expf(v[c] * yv) + 1.0f) : 0.f;
                 }
                 // R^T (bf16) into the operand image: sub-tile rr/64, K index rr%64
@@ -301,8 +317,13 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
                 unsigned char* rbase = Rs + eg * R_BYTES + (rr >> 6) * (BN * 128) + (rr & 7) * 2;
                 const int c16 = (rr & 63) >> 3;
 #pragma unroll
-                for (int c = 0; c < BN; ++c)
-                    *reinterpret_cast<unsigned short*>(rbase + c * 128 + ((c16 ^ (c & 7)) << 4)) = bf16_bits(v[c]);
+                for (int c = 0; c < CO; ++c) {
+                    const unsigned short hi = bf16_bits(v[c]);
+                    *reinterpret_cast<unsigned short*>(rbase + c * 128 + ((c16 ^ (c & 7)) << 4)) = hi;
+                    if constexpr (SPLIT)
+                        *reinterpret_cast<unsigned short*>(rbase + (c + CO) * 128 + ((c16 ^ ((c + CO) & 7)) << 4)) =
+                            bf16_bits(v[c] - __uint_as_float((uint32_t)hi << 16));
+                }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&rfull[eg]);
@@ -311,7 +332,7 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
             }
 
             // ---------------- backward accumulators: TMEM -> this CTA's partial [CN][ldw]
-            float* mine = p.partials + (size_t)blockIdx.x * ((size_t)BN * p.ldw);
+            float* mine = p.partials + (size_t)blockIdx.x * ((size_t)CO * p.ldw);
             if (my_tiles > 0) {
                 mbar_wait(tdone, 0);
                 tc_fence_after();
@@ -320,10 +341,16 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
                 const int j = ch * 128 + q * 32 + lane;
                 const uint32_t taddr = tmem_d2 + ((uint32_t)(q * 32) << 16) + ch * BN;
 #pragma unroll
-                for (int cb = 0; cb < NB; ++cb) {
+                for (int cb = 0; cb < CO / 16; ++cb) {
                     float t16[16];
                     if (my_tiles > 0) {
                         tmem_ld16(taddr + cb * 16, t16);
+                        if constexpr (SPLIT) {                 // + the lo-residual half
+                            float u16[16];
+                            tmem_ld16(taddr + CO + cb * 16, u16);
+#pragma unroll
+                            for (int e = 0; e < 16; ++e) t16[e] += u16[e];
+                        }
                     } else {
 #pragma unroll
                         for (int e = 0; e < 16; ++e) t16[e] = 0.f;
@@ -352,7 +379,7 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
 
     uint32_t gen = 0;
     grid_barrier(&p.hdr->barrier, gen);
-    const int n4 = (BN * p.ldw) >> 2;
+    const int n4 = (CO * p.ldw) >> 2;
     for (int i4 = (int)blockIdx.x * MB_THREADS + tid; i4 < n4; i4 += G * MB_THREADS) {
         float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
         const float4* src = reinterpret_cast<const float4*>(p.partials) + i4;
@@ -385,11 +412,15 @@ static size_t mc_bf16_smem(int dk, int BN, int stages) {
            (2 * MB_MAX_STAGES + 4 * MB_GROUPS + 2) * sizeof(uint64_t) + 16;
 }
 
+// hi + lo operand pairs (16 mantissa bits for parameters and residuals) for up to 16 model columns
+static bool mc_bf16_split(int CN) { return CN == 16 && getenv("EH_MC_BF16_PLAIN") == nullptr; }
+
 int mc_bf16_stages(int dk, int CN) {
     const int n_chunks = (dk + 127) / 128;
-    if (MB_GROUPS * CN + n_chunks * CN > 512) return 0;
+    const int BN = mc_bf16_split(CN) ? 2 * CN : CN;       // columns inside the tensor-core tiles
+    if (MB_GROUPS * BN + n_chunks * BN > 512) return 0;
     for (int s = MB_MAX_STAGES; s >= n_chunks && s >= 1; --s)
-        if (mc_bf16_smem(dk, CN, s) <= (size_t)227 * 1024) return s;
+        if (mc_bf16_smem(dk, BN, s) <= (size_t)227 * 1024) return s;
     return 0;
 }
 
@@ -407,10 +438,10 @@ static int make_map_bf16(CUtensorMap* map, const void* base, uint64_t inner, uin
     return EH_OK;
 }
 
-template <int NB>
+template <int NB, bool SPLIT>
 static int launch_mc_bf16(const McBf16Maps& maps, McBf16Params& p, int grid, cudaStream_t st) {
     const size_t smem = mc_bf16_smem(p.dk, 16 * NB, p.n_stages);
-    auto kern = mc_bf16_kernel<NB>;
+    auto kern = mc_bf16_kernel<NB, SPLIT>;
     static bool attr_done = false;
     if (!attr_done) {
         EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -451,7 +482,8 @@ int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, 
     EH_REQUIRE(fused_bytes >= need, "grad_mc(bf16): scratch too small (%zu < %zu)", fused_bytes, need);
     p.hdr = reinterpret_cast<GradScratchHdr*>(fused_scratch);
     p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(fused_scratch) + sizeof(GradScratchHdr));
-    return CN == 16 ? launch_mc_bf16<1>(maps, p, (int)grid, st) : launch_mc_bf16<2>(maps, p, (int)grid, st);
+    if (mc_bf16_split(CN)) return launch_mc_bf16<2, true>(maps, p, (int)grid, st);
+    return CN == 16 ? launch_mc_bf16<1, false>(maps, p, (int)grid, st) : launch_mc_bf16<2, false>(maps, p, (int)grid, st);
 }
 
 }  // namespace eh

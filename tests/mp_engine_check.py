@@ -63,7 +63,7 @@ def main():
         if ctx.is_root:
             ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0, model=eng.model)
             err = np.abs(res.betaset - ref.betaset).max() / max(1.0, np.abs(ref.betaset).max())
-            ok = (err <= ({"softmax": 5e-3, "softmax_bf16": 2e-2}.get(name, 1e-3)) and np.array_equal(res.n_collected, ref.n_collected)
+            ok = (err <= ({"softmax": 5e-3, "softmax_bf16": 5e-3}.get(name, 1e-3)) and np.array_equal(res.n_collected, ref.n_collected)
                   and np.array_equal(res.worker_timeset >= 0, ref.worker_timeset >= 0))
             print(f"[mp_engine_check] {name}: world={ctx.world} device={ctx.device} rel_err={err:.2e} "
                   f"round_ms={res.timeset.mean() * 1e3:.2f} {'OK' if ok else 'MISMATCH'}", flush=True)

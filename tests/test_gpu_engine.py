@@ -187,7 +187,7 @@ def test_engine_softmax_bf16_rows_matches_oracle_on_rounded_data():
     res = eng.run()
     ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl, beta0=eng.beta0, model=eng.model)
     scale = max(1.0, np.abs(ref.betaset).max())
-    assert np.abs(res.betaset - ref.betaset).max() <= 2e-2 * scale        # W and the residual are bf16 MMA operands
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-3 * scale        # hi + lo bf16 operand pairs for W and the residual
     assert np.array_equal(res.n_collected, ref.n_collected)
     ev = eng.evaluate(res)
     assert ev.training_loss[-1] < ev.training_loss[0]

@@ -274,7 +274,9 @@ def test_grad_mc_bf16_rows_all_tcgen05(rows, d, C, model):
     G2, _ = mc.grad_mc(Xs, ys, Wp, d, C, coeff=cf, model=model)
     assert torch.equal(G, G2)
     want = torch.zeros(d, C, dtype=torch.float64, device=DEV)
-    Wb = W.to(torch.bfloat16).double()
+    # up to 16 columns: parameters and residuals enter the MMAs as hi + lo bf16 pairs (16 mantissa bits)
+    split = C <= 16
+    Wb = W.double() if split else W.to(torch.bfloat16).double()
     for X, y, c in zip(Xs, ys, cf):
         P = X[:, :d].double() @ Wb
         if model == 2:
@@ -286,7 +288,7 @@ def test_grad_mc_bf16_rows_all_tcgen05(rows, d, C, model):
         want += X[:, :d].double().t() @ (c * R)
     got = mc.unpack_params(G, d, C).double()
     scale = max(1.0, want.abs().max().item())
-    assert (got - want).abs().max().item() <= 1.5e-2 * scale
+    assert (got - want).abs().max().item() <= (5e-4 if split else 1.5e-2) * scale
     assert torch.all(G[C:] == 0) and torch.all(G[:, d:] == 0)
 
 
