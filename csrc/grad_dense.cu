@@ -25,6 +25,10 @@
 
 namespace eh {
 
+// all-tcgen05 kernel for narrow bf16 rows (grad_mc_bf16.cu)
+int mc_bf16_stages(int dk, int CN);
+int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st, bool single_vector);
+
 // 16 bytes of a row as E floats: 4 fp32 values, or 8 bf16 values widened to fp32
 template <int E>
 __device__ __forceinline__ void unpack16(const uint4& q, float (&f)[E]) {
@@ -332,6 +336,23 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
             if (rc) return rc;
         }
         return EH_OK;
+    }
+    if (p.x_bf16 && n_jobs == 1 && p.ld >= 96 && p.ld <= 640 && !(p.ld > 384 && p.ld <= 512) &&
+        p.ld >= (p.d + 31) / 32 * 32 &&
+        mc_bf16_stages((p.d + 31) / 32 * 32, 16) > 0 && getenv("EH_BF16_CUDA_CORES") == nullptr) {
+        // narrow bf16 rows: both matrix-vector products on tcgen05 from one TMA tile (grad_mc_bf16.cu; beta and
+        // the residual enter as hi + lo bf16 pairs): 0.96 / 0.92 / 0.74 of HBM at 128 / 256 / 640 columns against
+        // 0.75 / 0.81 / 0.52 for the CUDA-core kernels (which keep 385..512 columns: 0.80 vs 0.77)
+        eh_mc_job m;
+        memset(&m, 0, sizeof(m));
+        for (int i = 0; i < j0->n_segs; ++i) {
+            m.d_X[i] = (const float*)j0->d_X[i]; m.d_y[i] = j0->d_y[i]; m.coeff[i] = j0->coeff[i];
+        }
+        m.d_W = j0->d_beta; m.d_out = j0->d_out; m.d_flag = j0->d_flag; m.d_beta_flag = j0->d_beta_flag; m.d_err = j0->d_err;
+        m.n_segs = j0->n_segs; m.rows_per_seg = j0->rows_per_seg; m.d = j0->d; m.ld = j0->ld;
+        m.ldw = (j0->d + 31) / 32 * 32; m.C = 1; m.model = (j0->model == EH_MODEL_LOGISTIC) ? 3 : 4;
+        m.stamp = j0->stamp; m.timeout_ns = j0->timeout_ns; m.x_bf16 = 1;
+        return mc_bf16_launch(&m, d_scratch, scratch_bytes, st, true);
     }
     if (p.x_bf16) {
         // bf16 rows: 8 columns per 16-byte vector, 256 vectors per row pass

@@ -57,6 +57,8 @@ struct McBf16Params {
     float* partials;
     int n_segs, rows_per_seg, tiles_per_seg;
     int d, dk, ldw, n_chunks, C, model, n_stages;
+    int w_rows;                      // rows of W that exist in memory (single-vector callers: 1, d floats long)
+    int out_rows;                    // rows of the result that are reduced and written (each d floats of ldw)
     uint32_t stamp, seq;
     unsigned long long timeout_ns;
 };
@@ -251,7 +253,7 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
             // ---------------- W^T as bf16 into the K-major SW128 operand image, one box per 64 columns
             for (int i = et; i < CO * p.n_chunks * 128; i += MB_GROUPS * 128) {
                 const int n = i / (p.n_chunks * 128), c = i % (p.n_chunks * 128);
-                const float w = (c < p.ldw) ? __ldcg(p.W + (size_t)n * p.ldw + c) : 0.f;
+                const float w = (n < p.w_rows && c < p.d) ? __ldcg(p.W + (size_t)n * p.ldw + c) : 0.f;
                 const int box = c >> 6, cc = c & 63;
                 unsigned char* at = Ws + (size_t)box * W_BOX + (cc & 7) * 2;
                 const unsigned short hi = bf16_bits(w);
@@ -307,10 +309,13 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
                     const int yc = (int)yv;
 #pragma unroll
                     for (int c = 0; c < CO; ++c) v[c] = valid ? cf * (v[c] * inv - (c == yc ? 1.f : 0.f)) : 0.f;
-                } else {
+                } else if (p.model == 3) {
 #pragma unroll
                     for (int c = 0; c < CO; ++c)
                         v[c] = (valid && c < p.C) ? cf * __fdividef(-yv, __expf(v[c] * yv) + 1.0f) : 0.f;
+                } else {                                   // linear regression per column: -2 (y - p)
+#pragma unroll
+                    for (int c = 0; c < CO; ++c) v[c] = (valid && c < p.C) ? cf * -2.0f * (yv - v[c]) : 0.f;
                 }
                 // R^T (bf16) into the operand image: sub-tile rr/64, K index rr%64
                 if (tl >= MB_GROUPS) mbar_wait(&rempty[eg], ((tl / MB_GROUPS) - 1) & 1);
@@ -332,7 +337,7 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
             }
 
             // ---------------- backward accumulators: TMEM -> this CTA's partial [CN][ldw]
-            float* mine = p.partials + (size_t)blockIdx.x * ((size_t)CO * p.ldw);
+            float* mine = p.partials + (size_t)blockIdx.x * ((size_t)p.out_rows * p.ldw);
             if (my_tiles > 0) {
                 mbar_wait(tdone, 0);
                 tc_fence_after();
@@ -357,7 +362,8 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
                     }
                     if (j < p.ldw) {
 #pragma unroll
-                        for (int e = 0; e < 16; ++e) __stcg(mine + (size_t)(cb * 16 + e) * p.ldw + j, (j < p.d) ? t16[e] : 0.f);
+                        for (int e = 0; e < 16; ++e)
+                            if (cb * 16 + e < p.out_rows) __stcg(mine + (size_t)(cb * 16 + e) * p.ldw + j, (j < p.d) ? t16[e] : 0.f);
                     }
                 }
             }
@@ -379,18 +385,26 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
 
     uint32_t gen = 0;
     grid_barrier(&p.hdr->barrier, gen);
-    const int n4 = (CO * p.ldw) >> 2;
+    const int n4 = (p.out_rows * p.ldw) >> 2;
     for (int i4 = (int)blockIdx.x * MB_THREADS + tid; i4 < n4; i4 += G * MB_THREADS) {
         float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
         const float4* src = reinterpret_cast<const float4*>(p.partials) + i4;
-        if ((i4 * 4) % p.ldw < p.n_chunks * 128) {
+        const int col = (i4 * 4) % p.ldw;
+        if (col < p.n_chunks * 128) {
 #pragma unroll 8
             for (int b = 0; b < G; ++b) {
                 const float4 t = __ldcg(src + (size_t)b * n4);
                 s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
             }
         }
-        reinterpret_cast<float4*>(p.out)[i4] = s;
+        if (p.out_rows == CO || col + 3 < p.d) {           // full [CN][ldw] result, or inside a d-float vector
+            reinterpret_cast<float4*>(p.out)[i4] = s;
+        } else {                                           // tail of a caller's d-float vector
+            float* o = p.out + (size_t)i4 * 4;
+            if (col + 0 < p.d) o[0] = s.x;
+            if (col + 1 < p.d) o[1] = s.y;
+            if (col + 2 < p.d) o[2] = s.z;
+        }
     }
     __syncthreads();
     if (tid == 0) {
@@ -452,7 +466,8 @@ static int launch_mc_bf16(const McBf16Maps& maps, McBf16Params& p, int grid, cud
 }
 
 // bf16 feature rows (eh_mc_job.x_bf16): `fused_scratch` = zero-initialised barrier header + per-CTA partials
-int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st) {
+// `single_vector`: W and the result are plain d-float vectors (the single-column dense entry point)
+int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st, bool single_vector) {
     const int CN = j->C <= 16 ? 16 : 32;
     const int dk = (j->d + 31) / 32 * 32;
     EH_REQUIRE((j->ld % 8) == 0 && j->ld >= dk, "grad_mc(bf16): rows must be padded to %d columns, ld %% 8 == 0 (ld=%d)", dk, j->ld);
@@ -473,12 +488,13 @@ int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, 
     p.W = j->d_W; p.out = j->d_out; p.flag = j->d_flag; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
     p.n_segs = j->n_segs; p.rows_per_seg = j->rows_per_seg; p.tiles_per_seg = (j->rows_per_seg + 127) / 128;
     p.d = j->d; p.dk = dk; p.ldw = j->ldw; p.n_chunks = (dk + 127) / 128; p.C = j->C; p.model = j->model;
+    p.w_rows = single_vector ? 1 : CN; p.out_rows = single_vector ? 1 : CN;
     p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     const long long n_tiles = (long long)p.n_segs * p.tiles_per_seg;
     long long grid = dev_info().sm_count;
     if (grid > n_tiles) grid = n_tiles;
-    const size_t need = sizeof(GradScratchHdr) + (size_t)grid * CN * p.ldw * sizeof(float);
+    const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.out_rows * p.ldw * sizeof(float);
     EH_REQUIRE(fused_bytes >= need, "grad_mc(bf16): scratch too small (%zu < %zu)", fused_bytes, need);
     p.hdr = reinterpret_cast<GradScratchHdr*>(fused_scratch);
     p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(fused_scratch) + sizeof(GradScratchHdr));

@@ -356,7 +356,7 @@ size_t mc_fused_scratch_bytes(int d, int CN);
 int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
 // bf16 rows, both products on tcgen05 (grad_mc_bf16.cu)
 int mc_bf16_stages(int dk, int CN);
-int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
+int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st, bool single_vector);
 // one-pass kernel on thread-block clusters (grad_mc_cluster.cu)
 bool mc_cluster_plan(int dk, int CN, int* cs_out, int* npc_out, int* stages_out);
 int mc_cluster_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, cudaStream_t st);
@@ -386,7 +386,8 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
     EH_REQUIRE(j && j->d_W && d_scratch, "grad_mc: null pointer");
     EH_REQUIRE(j->d_out || j->d_loss, "grad_mc: nothing to compute");
     EH_REQUIRE(j->C >= 1 && j->C <= 32, "grad_mc: C=%d classes not supported (1..32)", j->C);
-    EH_REQUIRE(j->model == 2 || j->model == 3, "grad_mc: model must be 2 (softmax) or 3 (batched logistic)");
+    EH_REQUIRE(j->model == 2 || j->model == 3 || (j->model == 4 && j->x_bf16),
+               "grad_mc: model must be 2 (softmax) or 3 (batched logistic); 4 (batched linear) needs bf16 rows");
     EH_REQUIRE(j->n_segs > 0 && j->n_segs <= EH_MAX_SEGS && j->rows_per_seg > 0 && j->d > 0, "grad_mc: bad shape");
     const int CN = j->C <= 16 ? 16 : 32, NB = CN / 16;
     const int dk = (j->d + 31) / 32 * 32;
@@ -400,7 +401,7 @@ extern "C" int eh_grad_mc(const eh_mc_job* j, void* d_scratch, size_t scratch_by
     if (j->x_bf16) {
         EH_REQUIRE(j->d_out && !j->d_loss, "grad_mc: bf16 rows are supported for the gradient call only");
         const size_t off = mc_twopass_scratch_bytes(j->rows_per_seg, j->d, CN);
-        return mc_bf16_launch(j, (char*)d_scratch + off, scratch_bytes - off, st);
+        return mc_bf16_launch(j, (char*)d_scratch + off, scratch_bytes - off, st, false);
     }
     // gradient of a narrow model: one pass over X, one launch (grad_mc_fused.cu)
     if (j->d_out && !j->d_loss && getenv("EH_MC_TWOPASS") == nullptr) {
