@@ -20,13 +20,16 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
         const int par = round & 1;
         const uint32_t stamp = (uint32_t)round + 1u;
         // dense single-vector messages of one shape are batched into one launch (<= 8 messages,
-        // <= 32 partitions); one-hot and multi-column messages get their own kernels
+        // <= 32 partitions), and so are one-hot messages; multi-column messages get their own kernels
         eh_grad_job batch[8];
-        int nb = 0, nb_segs = 0;
+        eh_grad_ell_job ebatch[8];
+        int nb = 0, nb_segs = 0, ne = 0, ne_segs = 0;
         auto flush = [&]() -> int {
-            if (nb == 0) return EH_OK;
-            int rc = eh_grad_dense_multi(batch, nb, plan->d_scratch, plan->scratch_bytes, stream);
+            int rc = EH_OK;
+            if (nb > 0) rc = eh_grad_dense_multi(batch, nb, plan->d_scratch, plan->scratch_bytes, stream);
             nb = 0; nb_segs = 0;
+            if (rc == EH_OK && ne > 0) rc = eh_grad_ell_multi(ebatch, ne, plan->d_scratch, plan->scratch_bytes, stream);
+            ne = 0; ne_segs = 0;
             return rc;
         };
         for (int q = 0; q < plan->n_jobs; ++q) {
@@ -82,8 +85,6 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 batch[nb++] = j;
                 nb_segs += j.n_segs;
             } else {
-                rc = flush();
-                if (rc) return rc;
                 eh_grad_ell_job j;
                 memset(&j, 0, sizeof(j));
                 for (int i = 0; i < wj.n_segs && i < EH_MAX_SEGS; ++i) {
@@ -94,7 +95,16 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.d_beta = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.nnz = wj.ld_or_nnz;
                 j.model = wj.model; j.bias_col = wj.bias_col; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
-                rc = eh_grad_ell(&j, plan->d_scratch, plan->scratch_bytes, stream);
+                const bool fits = nb == 0 && ne < 8 && ne_segs + j.n_segs <= 32 &&
+                                  (ne == 0 || (ebatch[0].d == j.d && ebatch[0].nnz == j.nnz &&
+                                               ebatch[0].rows_per_seg == j.rows_per_seg && ebatch[0].model == j.model &&
+                                               ebatch[0].bias_col == j.bias_col));
+                if (!fits) {
+                    rc = flush();
+                    if (rc) return rc;
+                }
+                ebatch[ne++] = j;
+                ne_segs += j.n_segs;
             }
             if (rc) return rc;
         }

@@ -22,7 +22,8 @@ namespace eh {
 
 constexpr int GE_THREADS = 512;
 constexpr int GE_TABLE = 2048;                 // per-CTA hot-column accumulators (direct-mapped)
-constexpr int GE_MAX_SEGS = EH_MAX_SEGS;
+constexpr int GE_MAX_SEGS = 32;                // partitions over all batched messages
+constexpr int GE_MAX_JOBS = 8;                 // messages batched into one launch (shared-memory variant)
 constexpr uint32_t GE_GO = 1, GE_SKIP = 2;
 
 struct EllScratchHdr {
@@ -47,6 +48,12 @@ struct EllParams {
     uint32_t stamp, seq;
     unsigned long long timeout_ns;
     float coeff[GE_MAX_SEGS];
+    // batched messages (shared-memory variant): job j owns CTAs [job_cta0[j], job_cta0[j+1]) and segments
+    // [job_seg0[j], job_seg0[j] + job_nsegs[j]) and writes job_out[j] / releases job_flag[j]
+    int n_jobs;
+    int job_cta0[GE_MAX_JOBS + 1], job_seg0[GE_MAX_JOBS], job_nsegs[GE_MAX_JOBS];
+    float* job_out[GE_MAX_JOBS];
+    uint32_t* job_flag[GE_MAX_JOBS];
 };
 
 __device__ __forceinline__ float ell_residual(int model, float p, float y) {
@@ -208,19 +215,24 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
         __syncthreads();
     }
 
-    const long long gwarp = (long long)b * (GES_THREADS / 32) + warp;
-    const long long nwarps = (long long)G * (GES_THREADS / 32);
+    // which batched message this CTA works for
+    int jb = 0;
+    while (jb + 1 < p.n_jobs && b >= p.job_cta0[jb + 1]) ++jb;
+    const int b0 = p.job_cta0[jb], Gj = p.job_cta0[jb + 1] - b0, bl = b - b0, seg0 = p.job_seg0[jb];
+    const long long job_rows = (long long)p.rows_per_seg * p.job_nsegs[jb];
+    const long long gwarp = (long long)bl * (GES_THREADS / 32) + warp;
+    const long long nwarps = (long long)Gj * (GES_THREADS / 32);
     float bias_acc = 0.f;
     constexpr int RW = 4;                      // rows in flight per warp: hides the index-load latency
-    for (long long row0 = gwarp * RW; row0 < p.rows; row0 += nwarps * RW) {
+    for (long long row0 = gwarp * RW; row0 < job_rows; row0 += nwarps * RW) {
         int cols[RW][2];
         float yv[RW], cf[RW], s[RW];
         const int32_t* rip[RW];
 #pragma unroll
         for (int r = 0; r < RW; ++r) {
             const long long row = row0 + r;
-            const bool valid = row < p.rows;
-            const int sg = valid ? (int)(row / p.rows_per_seg) : 0;
+            const bool valid = row < job_rows;
+            const int sg = seg0 + (valid ? (int)(row / p.rows_per_seg) : 0);
             const int lr = valid ? (int)(row % p.rows_per_seg) : 0;
             rip[r] = p.seg_idx[sg] + (size_t)lr * p.nnz;
             cols[r][0] = (valid && lane < p.nnz) ? __ldg(rip[r] + lane) : -1;
@@ -233,7 +245,7 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
             float t = 0.f;
             if (cols[r][0] >= 0) t += BETA_IN_SMEM ? bsm[cols[r][0]] : __ldcg(p.beta + cols[r][0]);
             if (cols[r][1] >= 0) t += BETA_IN_SMEM ? bsm[cols[r][1]] : __ldcg(p.beta + cols[r][1]);
-            if (p.nnz > 64 && row0 + r < p.rows)
+            if (p.nnz > 64 && row0 + r < job_rows)
                 for (int k = lane + 64; k < p.nnz; k += 32) {
                     const int c = __ldg(rip[r] + k);
                     t += BETA_IN_SMEM ? bsm[c] : __ldcg(p.beta + c);
@@ -255,7 +267,7 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
                     else atomicAdd(acc + cols[r][q], rs);
                 }
             }
-            if (p.nnz > 64 && row0 + r < p.rows)
+            if (p.nnz > 64 && row0 + r < job_rows)
                 for (int k = lane + 64; k < p.nnz; k += 32) {
                     const int c = __ldg(rip[r] + k);
                     if (c == p.bias_col) bias_acc += rs;
@@ -274,13 +286,14 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
     uint32_t gen = 0;
     grid_barrier(&p.hdr->barrier, gen);
 
-    // ordered reduction: CTA b owns a contiguous column range
-    const int chunk = (p.d + G - 1) / G;
-    const int c0 = b * chunk, c1 = min(p.d, c0 + chunk);
+    // ordered reduction per message: CTA bl of the message owns a contiguous column range
+    const int chunk = (p.d + Gj - 1) / Gj;
+    const int c0 = bl * chunk, c1 = min(p.d, c0 + chunk);
+    float* out = p.job_out[jb];
     for (int c = c0 + tid; c < c1; c += GES_THREADS) {
         float t = 0.f;
-        for (int g = 0; g < G; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
-        p.out[c] = t;
+        for (int g = b0; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
+        out[c] = t;
     }
     __syncthreads();
     if (tid == 0) {
@@ -290,7 +303,8 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
             p.hdr->barrier = 0;
             p.hdr->done = 0;
             __threadfence_system();
-            if (p.flag) st_release_sys(p.flag, p.stamp);
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);       // ordered by the fence above
         }
     }
 }
@@ -309,20 +323,51 @@ extern "C" size_t eh_grad_ell_scratch_bytes(int d) {
     return b;
 }
 
-extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
+// Up to GE_MAX_JOBS messages of one shape in ONE launch of the shared-memory variant (CTA ranges per message,
+// proportional to their partition counts); feature spaces too large for shared memory fall back to one
+// global-atomic launch per message.
+extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes,
+                                 void* stream) {
     using namespace eh;
-    EH_REQUIRE(j && j->d_beta && j->d_out && d_scratch, "grad_ell: null pointer");
-    EH_REQUIRE(j->n_segs > 0 && j->n_segs <= EH_MAX_SEGS, "grad_ell: n_segs out of range");
+    EH_REQUIRE(jobs && n_jobs >= 1 && n_jobs <= GE_MAX_JOBS && d_scratch, "grad_ell: bad job list (1..%d messages)", GE_MAX_JOBS);
+    const eh_grad_ell_job* j = &jobs[0];
+    EH_REQUIRE(j->d_beta, "grad_ell: null pointer");
     EH_REQUIRE(j->rows_per_seg > 0 && j->d > 0 && j->nnz > 0, "grad_ell: empty problem");
     EH_REQUIRE(scratch_bytes >= eh_grad_ell_scratch_bytes(j->d), "grad_ell: scratch too small");
+    const DevInfo& di = dev_info();
+    const size_t acc_bytes = (size_t)((j->d + 3) & ~3) * sizeof(float);
+    const bool smem_variant = acc_bytes <= GES_SMEM_LIMIT && getenv("EH_ELL_GLOBAL") == nullptr;
+    if (!smem_variant && n_jobs > 1) {
+        for (int q = 0; q < n_jobs; ++q) {
+            const int rc = eh_grad_ell_multi(&jobs[q], 1, d_scratch, scratch_bytes, stream);
+            if (rc) return rc;
+        }
+        return EH_OK;
+    }
     EllParams p;
     memset(&p, 0, sizeof(p));
-    for (int i = 0; i < j->n_segs; ++i) {
-        EH_REQUIRE(j->d_idx[i] && j->d_y[i], "grad_ell: null segment %d", i);
-        p.seg_idx[i] = j->d_idx[i];
-        p.seg_y[i] = j->d_y[i];
-        p.coeff[i] = j->coeff[i];
+    int nseg = 0;
+    for (int q = 0; q < n_jobs; ++q) {
+        const eh_grad_ell_job* jq = &jobs[q];
+        EH_REQUIRE(jq->d_out, "grad_ell: null destination");
+        EH_REQUIRE(jq->n_segs > 0 && jq->n_segs <= EH_MAX_SEGS, "grad_ell: n_segs out of range");
+        EH_REQUIRE(jq->d == j->d && jq->nnz == j->nnz && jq->rows_per_seg == j->rows_per_seg && jq->model == j->model &&
+                       jq->bias_col == j->bias_col && jq->d_beta == j->d_beta && jq->d_beta_flag == j->d_beta_flag &&
+                       jq->stamp == j->stamp,
+                   "grad_ell: batched messages must share shape, model, parameters and stamp");
+        EH_REQUIRE(nseg + jq->n_segs <= GE_MAX_SEGS, "grad_ell: more than %d partitions in one batch", GE_MAX_SEGS);
+        p.job_seg0[q] = nseg;
+        p.job_nsegs[q] = jq->n_segs;
+        p.job_out[q] = jq->d_out;
+        p.job_flag[q] = jq->d_flag;
+        for (int i = 0; i < jq->n_segs; ++i, ++nseg) {
+            EH_REQUIRE(jq->d_idx[i] && jq->d_y[i], "grad_ell: null segment %d", i);
+            p.seg_idx[nseg] = jq->d_idx[i];
+            p.seg_y[nseg] = jq->d_y[i];
+            p.coeff[nseg] = jq->coeff[i];
+        }
     }
+    p.n_jobs = n_jobs;
     p.beta = j->d_beta; p.out = j->d_out;
     p.flag = j->d_flag; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
     p.hdr = reinterpret_cast<EllScratchHdr*>(d_scratch);
@@ -331,16 +376,23 @@ extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scr
     p.rows_per_seg = j->rows_per_seg; p.n_segs = j->n_segs;
     p.model = j->model; p.bias_col = j->bias_col; p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
-    const DevInfo& di = dev_info();
-    const size_t acc_bytes = (size_t)((j->d + 3) & ~3) * sizeof(float);
-    if (acc_bytes <= GES_SMEM_LIMIT && getenv("EH_ELL_GLOBAL") == nullptr) {
-        // shared-memory variant
+    if (smem_variant) {
         const bool both = 2 * acc_bytes <= GES_SMEM_LIMIT;
         const size_t smem = both ? 2 * acc_bytes : acc_bytes;
+        // CTAs per message in proportion to its rows (32 rows of work per warp at least), every message >= 1
+        const long long total_rows = (long long)j->rows_per_seg * nseg;
         long long grid = di.sm_count;
-        const long long want = (p.rows * 32 + GES_THREADS - 1) / GES_THREADS;
+        const long long want = (total_rows * 32 + GES_THREADS - 1) / GES_THREADS;
         if (grid > want) grid = want;
-        if (grid < 1) grid = 1;
+        if (grid < n_jobs) grid = n_jobs;
+        const long long spare = grid - n_jobs;
+        int used = 0;
+        p.job_cta0[0] = 0;
+        for (int q = 0; q < n_jobs; ++q) {
+            used += 1 + (int)(spare * p.job_nsegs[q] / nseg);
+            p.job_cta0[q + 1] = used;
+        }
+        grid = used;
         float* partials = p.gacc;
         EH_REQUIRE(scratch_bytes >= sizeof(EllScratchHdr) + (size_t)grid * j->d * sizeof(float),
                    "grad_ell: scratch too small for the shared-memory variant");
@@ -366,4 +418,9 @@ extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scr
     void* args[] = {(void*)&p};
     { int lrc = launch_grid_sync((const void*)grad_ell_kernel, dim3((unsigned)grid), dim3(GE_THREADS), args, 0, (cudaStream_t)stream); if (lrc) return lrc; }
     return EH_OK;
+}
+
+extern "C" int eh_grad_ell(const eh_grad_ell_job* j, void* d_scratch, size_t scratch_bytes, void* stream) {
+    EH_REQUIRE(j && j->d_out, "grad_ell: null pointer");
+    return eh_grad_ell_multi(j, 1, d_scratch, scratch_bytes, stream);
 }

@@ -136,6 +136,7 @@ def _declare(lib):
         "eh_grad_mc": (i32, [P(McJob), vp, sz, vp]),
         "eh_grad_ell_scratch_bytes": (sz, [i32]),
         "eh_grad_ell": (i32, [P(GradEllJob), vp, sz, vp]),
+        "eh_grad_ell_multi": (i32, [P(GradEllJob), i32, vp, sz, vp]),
         "eh_decoder_scratch_bytes": (sz, []),
         "eh_decoder_round": (i32, [P(DecoderDesc), i32, i32, vp]),
         "eh_decoder_publish": (i32, [P(DecoderDesc), i32, vp]),

@@ -107,6 +107,12 @@ def launch_ell(job: GradEllJob, scratch: Scratch, stream: Optional[int] = None) 
                             stream_ptr() if stream is None else stream), "eh_grad_ell")
 
 
+def launch_ell_multi(jobs: Sequence[GradEllJob], scratch: Scratch, stream: Optional[int] = None) -> None:
+    arr = (GradEllJob * len(jobs))(*jobs)
+    check(lib().eh_grad_ell_multi(arr, len(jobs), scratch.ptr(), scratch.nbytes,
+                                  stream_ptr() if stream is None else stream), "eh_grad_ell_multi")
+
+
 def _aslist(x):
     return list(x) if isinstance(x, (list, tuple)) else [x]
 

@@ -143,6 +143,10 @@ typedef struct eh_grad_ell_job {
 
 size_t eh_grad_ell_scratch_bytes(int d);
 int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
+/* Up to 8 one-hot messages of identical shape (same d, nnz, rows_per_seg, model, bias_col, parameters, stamp;
+ * at most 32 partitions in total) in ONE launch when the gradient fits in shared memory (CTA ranges per
+ * message); otherwise one launch per message. */
+int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes, void* stream);
 
 /* Multi-column models on the tensor cores (tcgen05.mma kind::tf32 for both products): softmax
  * regression with C classes (model 2, labels 0..C-1) and C independent logistic columns on the

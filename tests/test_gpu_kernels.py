@@ -69,6 +69,28 @@ def test_grad_ell_matches_reference(model):
     assert (g.double() - want).abs().max().item() <= 5e-4 * max(1.0, want.abs().max().item())
 
 
+@pytest.mark.parametrize("d", [5000, 70000])
+def test_grad_ell_multi_batches_messages_in_one_launch(d):
+    """Several one-hot messages (different partition counts / coefficients) in one launch; d = 70000 does
+    not fit in shared memory and takes the per-message fallback."""
+    from erasurehead_b200.data import generate_onehot
+    from erasurehead_b200.ops import grad
+    ds = generate_onehot(5 * 600, d, 19, 5, seed=2)
+    idxs = [torch.from_numpy(ds.ell(p)).to(DEV) for p in range(5)]
+    ys = [torch.tensor(ds.labels(p), dtype=torch.float32, device=DEV) for p in range(5)]
+    beta = torch.randn(d, device=DEV) * 0.3
+    msgs = [([0], [1.0]), ([1, 2, 3], [0.5, -2.0, 1.5]), ([4, 0], [1.0, 1.0])]
+    outs = [torch.full((d,), float("nan"), device=DEV) for _ in msgs]
+    sc = grad.ell_scratch(d, DEV)
+    jobs = [grad.make_ell_job([idxs[p] for p in ps], [ys[p] for p in ps], beta.data_ptr(), o.data_ptr(), d, cf, 0, d - 1)
+            for (ps, cf), o in zip(msgs, outs)]
+    grad.launch_ell_multi(jobs, sc)
+    torch.cuda.synchronize()
+    for (ps, cf), o in zip(msgs, outs):
+        want = sum(ref_grad(torch.tensor(ds.parts[p].toarray(), device=DEV), ys[p], beta, c, 0) for p, c in zip(ps, cf))
+        assert (o.double() - want).abs().max().item() <= 5e-4 * max(1.0, want.abs().max().item())
+
+
 def test_margins_loss_and_auc():
     from erasurehead_b200.ops import metrics as mops
     torch.manual_seed(1)
