@@ -119,6 +119,25 @@ def bench_sweep(ctx, a):
                        "mean_collected": float(res.n_collected.mean())})
 
 
+def bench_sweep_nccl(ctx, a):
+    """Round time of the NCCL + cuBLAS arm (B2) for the sweep's schemes: a gather is a collective, so every
+    message is waited for whatever the stop rule says; with the rounds-to-target of the product run (the
+    iterates are the same) this gives B2's time to target."""
+    from erasurehead_b200.parallel.nccl_baseline import NcclBaselineEngine
+    n, d, rows_pp = 8, 1024, a.rows_sweep
+    for scheme, s, k in (("naive", 0, 0), ("coded", 2, 0), ("approx", 1, 4), ("approx", 3, 2)):
+        cfg = mkcfg(scheme, n, s, n * rows_pp, d, k=k, rounds=40, synthetic=True, seed=1, delay_scale=a.delay_scale,
+                    eta0=a.eta0)
+        eng = NcclBaselineEngine(cfg, None, ctx=ctx)
+        ms = timed_rounds(ctx, eng, 3, 30)
+        emit(ctx, {"config": "delay_sweep", "impl": "nccl", "scheme": scheme, "s": s, "n_collect": k, "gpus": ctx.world,
+                   "n_workers": n, "rows_per_partition": rows_pp, "d": d, "delay": f"exp({a.delay_scale}s)",
+                   "mean_round_ms": ms})
+        eng.close()
+        del eng
+        torch.cuda.empty_cache()
+
+
 def bench_amazon(ctx, a):
     n, s, P = 8, 1, 3
     rows, d, nnz = 26215, 241915, 44
@@ -211,6 +230,8 @@ if __name__ == "__main__":
         bench_exact(ctx, a)
     if "sweep" in which:
         bench_sweep(ctx, a)
+    if "sweep_nccl" in which:
+        bench_sweep_nccl(ctx, a)
     if "amazon" in which:
         bench_amazon(ctx, a)
     if "multi" in which:
