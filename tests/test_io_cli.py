@@ -83,6 +83,15 @@ def test_cli_end_to_end_dense(tmp_path, capsys, scheme_args, prefix, files):
     assert ">>> At Iteration 0" in txt
 
 
+def test_cli_synthetic_without_files_or_gpu(tmp_path, capsys):
+    """README quick-start: --synthetic needs no data files; without a GPU the host generator stands in."""
+    argv = f"9 1600 12 {tmp_path}/nowhere 0 artificial 1 1 0 3 6 1 AGD --synthetic --rounds=4 --gpus=-1 --output-dir={tmp_path}/out/".split()
+    out = cli.run(parse_argv(argv))
+    assert os.path.exists(f"{tmp_path}/out/approx_acc_1_6_training_loss.dat")
+    assert "Iteration 3: Train Loss =" in capsys.readouterr().out
+    assert out["results_dir"] == f"{tmp_path}/out/"
+
+
 def test_cli_sparse_partial_and_compat_names(tmp_path):
     n, s, P = 4, 1, 3
     ds = generate_onehot(8 * 50, 120, 7, (P - s) * n, seed=3)
