@@ -152,11 +152,10 @@ class Engine:
                 segs = [sg for sg in spec.segments[w] if sg.msg == kind]
                 if not segs:
                     continue
-                for c0 in range(0, len(segs), _lib.EH_MAX_SEGS):
-                    if c0 > 0:
-                        raise NotImplementedError(
-                            f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
-                            "use fewer partitions per worker")
+                if len(segs) > _lib.EH_MAX_SEGS:
+                    raise NotImplementedError(
+                        f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
+                        "use fewer partitions per worker")
                 j = _lib.WorkerJob()
                 jkind = (4 if self.bf16 else 2) if self.mc else (1 if self.sparse else (3 if self.bf16 else 0))
                 j.worker, j.msg, j.sparse, j.model = w, kind, jkind, self.model.device_id
