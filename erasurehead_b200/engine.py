@@ -518,7 +518,15 @@ class Engine:
                 rows += Xp.shape[0]
             tr[i] = tot / rows
             te[i] = float(mc.loss_mc(Xt, yt, Wp, d, C_, self.model.device_id).item()) / Xt.shape[0]
-        return results.Evaluation(tr, te, None)
+        # test accuracy: margins of all classes through the tensor-core evaluation kernel, argmax per row
+        from .ops import metrics as mops
+        acc = np.zeros(R)
+        for i in range(R):
+            Wi = torch.zeros((C_, _pad32(d)), dtype=torch.float32, device=dev)
+            Wi[:, :d] = torch.from_numpy(np.ascontiguousarray(betaset[i].T)).to(dev)
+            _, M = mops.eval_tc(Xt, Wi, None, d=d, want_margins=True)
+            acc[i] = float((M[:, :C_].argmax(dim=1) == yt.long()).float().mean().item())
+        return results.Evaluation(tr, te, None, acc)
 
     def _evaluate_gpu(self, betaset: np.ndarray):
         from . import results
@@ -561,7 +569,11 @@ class Engine:
         if self.model.has_auc:
             Pcol = Pt.t().contiguous()
             auc = torch.stack([mops.auc(Pcol[i], yt) for i in range(R)]).cpu().numpy()
-        return results.Evaluation(tr.cpu().numpy(), te.cpu().numpy(), auc)
+        acc = None
+        if self.model.name != "linear":
+            pred = torch.where(Pt[:, :R] > 0, 1.0, -1.0)
+            acc = (pred == yt[:, None]).float().mean(dim=0).cpu().numpy().astype(np.float64)
+        return results.Evaluation(tr.cpu().numpy(), te.cpu().numpy(), auc, acc)
 
     def _device_test(self):
         torch = self.torch

@@ -24,6 +24,7 @@ class Evaluation:
     training_loss: np.ndarray
     testing_loss: np.ndarray
     auc: Optional[np.ndarray]
+    accuracy: Optional[np.ndarray] = None      # test accuracy per iterate (classification models; not in the reference)
 
 
 def evaluate_host(model, data, betaset: np.ndarray, n_eval_parts=None) -> Evaluation:
@@ -33,6 +34,7 @@ def evaluate_host(model, data, betaset: np.ndarray, n_eval_parts=None) -> Evalua
     R = betaset.shape[0]
     tr, te = np.zeros(R), np.zeros(R)
     auc = np.zeros(R) if model.has_auc else None
+    acc = None if model.name == "linear" else np.zeros(R)
     if betaset.ndim == 2:
         P_tr = np.asarray(X_tr.dot(betaset.T))
         P_te = np.asarray(X_te.dot(betaset.T))
@@ -41,11 +43,16 @@ def evaluate_host(model, data, betaset: np.ndarray, n_eval_parts=None) -> Evalua
             te[i] = model.loss(y_te, P_te[:, i])
             if auc is not None:
                 auc[i] = metrics.roc_auc(y_te, P_te[:, i])
+            if acc is not None:
+                acc[i] = float(np.mean(np.where(P_te[:, i] > 0, 1.0, -1.0) == y_te))
     else:
         for i in range(R):
             tr[i] = model.loss(y_tr, np.asarray(X_tr.dot(betaset[i])))
-            te[i] = model.loss(y_te, np.asarray(X_te.dot(betaset[i])))
-    return Evaluation(tr, te, auc)
+            M = np.asarray(X_te.dot(betaset[i]))
+            te[i] = model.loss(y_te, M)
+            if acc is not None:
+                acc[i] = float(np.mean(np.argmax(M, axis=1) == y_te.astype(np.int64)))
+    return Evaluation(tr, te, auc, acc)
 
 
 def print_table(ev: Evaluation, timeset: np.ndarray, metric: str = "loss", file=None) -> None:
@@ -76,6 +83,9 @@ def write_results(out_dir: str, prefix: str, ev: Optional[Evaluation], timeset, 
         np.save(j("testing_loss.npy"), ev.testing_loss)
         if ev.auc is not None:
             np.save(j("auc.npy"), ev.auc)
+        if ev.accuracy is not None and not compat:
+            io.save_vector(ev.accuracy, j("accuracy.dat"))
+            np.save(j("accuracy.npy"), ev.accuracy)
     io.save_vector(timeset, j("timeset.dat"))
     io.save_matrix(worker_timeset, j("worker_timeset.dat"))
     np.save(j("timeset.npy"), np.asarray(timeset))

@@ -59,6 +59,7 @@ def test_engine_matches_oracle(scheme, kw, rule):
     assert np.allclose(ev.training_loss, evh.training_loss, rtol=2e-3, atol=1e-4)
     assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=2e-3, atol=1e-4)
     assert np.allclose(ev.auc, evh.auc, atol=3e-3)
+    assert np.allclose(ev.accuracy, evh.accuracy, atol=5e-3)
     eng.cfg.eval_precision = "fp32"
     ev32 = eng.evaluate(res)
     assert np.allclose(ev32.training_loss, evh.training_loss, rtol=2e-4, atol=1e-5)
@@ -163,6 +164,7 @@ def test_engine_softmax_multiclass_matches_oracle():
     evh = results.evaluate_host(eng.model, data, res.betaset)
     assert np.allclose(ev.training_loss, evh.training_loss, rtol=3e-3)
     assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=3e-3)
+    assert np.allclose(ev.accuracy, evh.accuracy, atol=5e-3) and ev.accuracy[-1] > 1.5 / C_
     assert ev.training_loss[-1] < ev.training_loss[0]
     eng.close()
     # exact coded scheme on the same data: decode weights act on the flat multi-column vector
