@@ -633,6 +633,8 @@ class Engine:
                     rec["test_loss"] = float(ev.testing_loss[r])
                     if ev.auc is not None:
                         rec["auc"] = float(ev.auc[r])
+                    if getattr(ev, "accuracy", None) is not None:
+                        rec["test_accuracy"] = float(ev.accuracy[r])
                 f.write(json.dumps(rec) + "\n")
 
     def close(self) -> None:
