@@ -267,6 +267,23 @@ def test_engine_bf16_storage_matches_oracle_on_rounded_data():
     eng.close()
 
 
+@pytest.mark.parametrize("model", ["logistic", "linear"])
+def test_engine_narrow_bf16_rows_take_the_tensor_core_kernel(model):
+    """One worker per GPU and narrow bf16 rows: the single-column gradient runs on the all-tcgen05 kernel
+    (one message per launch); same oracle agreement as the CUDA-core bf16 path."""
+    cfg = mk("naive", n=1, s=0, d=200, rows=3000, dtype="bf16", model=model, eta0=0.5 if model == "linear" else 10.0)
+    task = "linear" if model == "linear" else "logistic"
+    data = generate_gmm(cfg.n_rows, cfg.n_cols, 1, seed=2, task=task)
+    data.parts = [torch.from_numpy(p).to(torch.bfloat16).double().numpy() for p in data.parts]
+    dl = spaced_delays(cfg.rounds, 1, seed=1)
+    eng = Engine(cfg, data, delays=dl)
+    assert eng.bf16 and eng.n_jobs == 1
+    res = eng.run()
+    ref = oracle.run_rounds(cfg, build_scheme(cfg), data, dl, beta0=eng.beta0, model=eng.model)
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-4 * max(1.0, np.abs(ref.betaset).max())
+    eng.close()
+
+
 def test_cuda_graph_mode_matches_stream_mode():
     """The whole run captured into one CUDA graph gives the same trajectory."""
     for scheme, kw in (("approx", dict(s=1, k=5)), ("coded", dict(s=2, seed=3)), ("partial_coded", dict(n=4, s=1, P=4, rows=12 * 160, seed=2))):
