@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Baseline B1 vs the product on the SAME data files and CLI arguments.
 
-Runs (a) the patched reference (baseline/_ref_py3, its own drivers, CPU, float64) over the
+Runs (a) the unmodified reference (baseline/_ref via py2run.py, its own drivers, CPU, float64) over the
 mpi4py subset and (b) this framework (`main.py`, GPU if present) for a small dense AGC / coded
 configuration that the reference can load (its loader is np.loadtxt), and prints one JSON line
 per arm with the mean per-iteration time from the `*_timeset.dat` files both write.

@@ -47,6 +47,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--beta-push", default="p2p", choices=["p2p", "multicast"])
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"], help="feature storage (headline: fp32)")
+    ap.add_argument("--ref-rows", type=int, default=1024,
+                    help="rows per partition of the reference arm and of the repo arm's `matched` block")
+    ap.add_argument("--no-covtype", action="store_true", help="skip the Covertype-shaped comparison block")
+    ap.add_argument("--no-matched", action="store_true", help="skip the runs at the reference arm's size")
     return ap.parse_args()
 
 
@@ -100,9 +104,12 @@ class ClockSampler:
 
 
 def reference_arm(args):
-    """Run the UNMODIFIED reference (baseline/_ref) through its own CLI, if it can run at all."""
+    """Run the UNMODIFIED reference (baseline/_ref) through its own CLI on the box's CPUs.  Under
+    torchrun only rank 0 works (the reference starts its own 2N+1 processes); the others exit."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
     from baseline.reference_arm import run_reference
-    print(json.dumps(run_reference(args)))
+    print(json.dumps(run_reference(args)), flush=True)
     return 0
 
 
