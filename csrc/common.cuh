@@ -37,6 +37,19 @@ struct DevInfo {
     int coop = 0;
 };
 const DevInfo& dev_info();
+// SMs that the gradient (worker) kernels may fill on the current device: all of them, minus the SMs
+// reserved for a decoder that runs concurrently on its own stream (eh_set_reserved_sms).
+int worker_sms();
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies per device: remember it per device
+#define EH_SET_MAX_SMEM(kern, bytes)                                                              \
+    do {                                                                                          \
+        static bool done__[64] = {false};                                                         \
+        const int dv__ = eh::dev_info().device;                                                   \
+        if (dv__ < 0 || dv__ >= 64 || !done__[dv__]) {                                            \
+            EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            if (dv__ >= 0 && dv__ < 64) done__[dv__] = true;                                      \
+        }                                                                                         \
+    } while (0)
 // Process-wide launch sequence number for the decision word of the cooperative gradient kernels.
 uint32_t next_launch_seq();
 // Launch a kernel whose CTAs wait on one another (device-wide barrier).  Cooperative by default so
@@ -54,6 +67,8 @@ enum CtlIndex {
     CTL_BETA_FLAG = 0,   // round+1 once beta of that round is readable in beta[round&1]
     CTL_ERROR     = 1,   // sticky error code (watchdogs)
     CTL_DECISION  = 2,   // worker kernel: (stamp<<1 | stale) decision broadcast by CTA 0
+    CTL_PING      = 3,   // clock alignment: sequence number stored by the root into a peer's workspace
+    CTL_PONG      = 4,   // clock alignment: peer's answer in the root's workspace (v = seq, bytes 8..15 = peer clock)
     CTL_COUNT     = 8,
 };
 
@@ -76,6 +91,18 @@ __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
 // (fence + relaxed stores form the release pattern; a release store per flag would fence every time)
 __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Arrival record of a message: a 16-byte (in the workspace: 128-byte) record whose word 0 is the round stamp
+// and whose bytes 8..15 hold the publishing GPU's %globaltimer at the moment the message was complete
+// -- the device-side analogue of the instant before the reference worker's sleep-then-Isend
+// (approximate_coding.py:198-207).  Store the time BEFORE the fence / release that publishes the stamp.
+__device__ __forceinline__ void st_arrival_time(uint32_t* flag) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(flag + 2), "l"(globaltimer()) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_arrival_time(const uint32_t* flag) {
+    uint64_t t;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(t) : "l"(flag + 2) : "memory");
+    return t;
 }
 // one store, delivered by the NVSwitch to every GPU bound to the multicast object (NVLS)
 __device__ __forceinline__ void multimem_st_v4(float* mc_addr, const float4& v) {

@@ -6,15 +6,24 @@
 // (approximate_coding.py:136-180, coded.py:133-166, partial_coded.py:170-205,
 // naive.py:112-124).  Here it is ONE kernel:
 //
-//   phase 1  (CTA 0, warp 0) polls the arrival flags that worker kernels on any GPU publish
-//            with st.release.sys, adds the injected message delay (delays.py), consumes arrivals
-//            in ready-time order, evaluates the stop rule after each one and derives the decode
-//            weights (table lookup by combinadic rank, or an in-kernel pivoted elimination);
+//   phase 1  (CTA 0, warp 0) polls the arrival records that worker kernels on any GPU publish
+//            with st.release.sys.  A record carries the worker GPU's clock at the moment the
+//            message was complete; the message becomes ready at  completion + injected delay
+//            (delays.py) -- the reference worker's compute, sleep, Isend order
+//            (approximate_coding.py:194-207) -- on the decoder's clock (per-GPU offsets measured
+//            at set-up, eh_clock_sync_*).  Arrivals are consumed in ready-time order, the stop
+//            rule is evaluated after each one and the decode weights are derived (table lookup by
+//            combinadic rank, or an in-kernel pivoted elimination);
 //   phase 2  (all CTAs) forms g = sum_w a_w * slot_w in float64, applies the update to the
 //            float64 master copy, appends the iterate to betaset and pushes the float32
 //            parameters into every GPU's workspace over NVLink (peer stores);
 //   phase 3  (last CTA) releases the parameter flag of the next round on every GPU and closes
 //            the round's timers.
+//
+// The kernel is a small grid (desc.dec_ctas CTAs) meant for its own high-priority stream next to
+// the gradient kernels of the same GPU, which leave that many SMs free (eh_set_reserved_sms): the
+// master only waits while the workers compute, as rank 0 of the reference does
+// (approximate_coding.py:144-158), so a round costs max(compute, stop-rule wait), not their sum.
 //
 // Stragglers are never waited for: once the stop rule fires the late messages of this round
 // are simply never read (their stamps no longer match), so the reference's stale-buffer hazards
@@ -24,7 +33,7 @@
 
 namespace eh {
 
-constexpr int DEC_THREADS = 256;
+constexpr int DEC_THREADS = 512;
 constexpr uint64_t NEVER = ~0ull;
 
 struct DecScratch {
@@ -91,10 +100,19 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
 #pragma unroll
                 for (int m = 0; m < EH_MAX_MSGS; ++m) {
                     if (!drain && ent[q][m].state == 0) {
-                        const uint32_t f = ld_acquire_sys(ws_flag(ws0, D.lay, lane + 32 * q, m));
+                        const int w = lane + 32 * q;
+                        const uint32_t* rec = ws_flag(ws0, D.lay, w, m);
+                        const uint32_t f = ld_acquire_sys(rec);
                         if (f == stamp) {
                             ent[q][m].state = 1;
-                            ent[q][m].ready = (dl[q] == NEVER) ? NEVER : now + dl[q];
+                            // completion time on this GPU's clock, clamped into [round start, now]
+                            uint64_t done = ld_arrival_time(rec);
+                            if (D.d_clock_off) done -= (uint64_t)D.d_clock_off[w];
+                            if ((int64_t)(done - t_start) < 0) done = t_start;
+                            if (done > now) done = now;
+                            ent[q][m].ready = (dl[q] == NEVER) ? NEVER : done + dl[q];
+                            if (D.d_done && m == EH_MSG_CODED)
+                                D.d_done[(size_t)r * n + w] = (double)(done - t_start) * 1e-9;
                         }
                     }
                 }
@@ -243,7 +261,19 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
         const int nxt = (round + 1) & 1;
         for (int c4 = blockIdx.x * DEC_THREADS + tid; c4 < d4; c4 += gridDim.x * DEC_THREADS) {
             double g[4] = {0.0, 0.0, 0.0, 0.0};
-            for (int q = 0; q < nsrc; ++q) {
+            int q = 0;
+            for (; q + 4 <= nsrc; q += 4) {            // four loads in flight, summed in source order
+                float4 t[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) t[u] = __ldcg(reinterpret_cast<const float4*>(s_src[q + u]) + c4);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const double a = s_wt[q + u];
+                    g[0] += a * (double)t[u].x; g[1] += a * (double)t[u].y;
+                    g[2] += a * (double)t[u].z; g[3] += a * (double)t[u].w;
+                }
+            }
+            for (; q < nsrc; ++q) {
                 const float4 t = __ldcg(reinterpret_cast<const float4*>(s_src[q]) + c4);
                 const double a = s_wt[q];
                 g[0] += a * (double)t.x; g[1] += a * (double)t.y; g[2] += a * (double)t.z; g[3] += a * (double)t.w;
@@ -332,6 +362,12 @@ __global__ void publish_flag_kernel(const eh_decoder_desc D, const int round) {
 
 extern "C" size_t eh_decoder_scratch_bytes(void) { return sizeof(eh::DecScratch); }
 
+// CTAs (= SMs to reserve) a decoder for d_pad parameters wants: 2048 float4 columns per CTA, 1..16
+extern "C" int eh_decoder_ctas(int d_pad) {
+    int c = (d_pad / 4 + 4 * eh::DEC_THREADS - 1) / (4 * eh::DEC_THREADS);
+    return c < 1 ? 1 : (c > 16 ? 16 : c);
+}
+
 static int check_desc(const eh_decoder_desc* D) {
     using namespace eh;
     EH_REQUIRE(D, "decoder: null descriptor");
@@ -354,12 +390,14 @@ extern "C" int eh_decoder_round(const eh_decoder_desc* D, int round, int r, void
     if (rc) return rc;
     const DevInfo& di = dev_info();
     int grid = (D->d_pad / 4 + DEC_THREADS - 1) / DEC_THREADS;
+    const int cap = D->dec_ctas > 0 ? D->dec_ctas : di.sm_count;
+    if (grid > cap) grid = cap;
     if (grid > di.sm_count) grid = di.sm_count;
     if (grid < 1) grid = 1;
-    eh_decoder_desc desc = *D;
-    int round_ = round, r_ = r;
-    void* args[] = {(void*)&desc, (void*)&round_, (void*)&r_};
-    { int lrc = launch_grid_sync((const void*)decoder_round_kernel, dim3(grid), dim3(DEC_THREADS), args, 0, (cudaStream_t)stream); if (lrc) return lrc; }
+    // CTAs > 0 only wait for CTA 0 (which is dispatched first) and nobody waits for them, so an ordinary
+    // launch is enough; the grid is small so that it fits next to the gradient kernels of this GPU
+    decoder_round_kernel<<<grid, DEC_THREADS, 0, (cudaStream_t)stream>>>(*D, round, r);
+    EH_CUDA(cudaGetLastError());
     return EH_OK;
 }
 

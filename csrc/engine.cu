@@ -1,5 +1,9 @@
 // Native round loop (see eh_run_rounds in erasurehead.h).
 //
+// With plan->dec_stream set (root rank) the decoder kernels go to their own stream and overlap the
+// gradient kernels of the same round on this GPU; the two streams are ordered against each other only
+// through the stamped flags, plus one event fork at the start and one join at the end of the call.
+//
 // The host only *enqueues*: all cross-GPU ordering is carried by the stamped flags in the
 // peer-mapped workspaces (worker kernels spin on the parameter flag, the decoder kernel spins on
 // arrival flags), so `n_rounds` rounds are in flight on every GPU's stream with no host
@@ -15,6 +19,15 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
     const eh_ws_layout& lay = plan->lay;
     uint32_t* beta_flag = ws_beta_flag(plan->d_ws_local, lay);
     uint32_t* err = ws_error(plan->d_ws_local, lay);
+    // decoder on its own stream: fork after everything already enqueued on `stream`, join at the end
+    cudaStream_t dec_stream = (cudaStream_t)stream;
+    const bool forked = plan->decoder && plan->dec_stream && plan->dec_stream != stream && n_rounds > 0;
+    if (forked) {
+        EH_REQUIRE(plan->ev_fork && plan->ev_join, "run_rounds: dec_stream needs ev_fork / ev_join");
+        dec_stream = (cudaStream_t)plan->dec_stream;
+        EH_CUDA(cudaEventRecord((cudaEvent_t)plan->ev_fork, (cudaStream_t)stream));
+        EH_CUDA(cudaStreamWaitEvent(dec_stream, (cudaEvent_t)plan->ev_fork, 0));
+    }
     for (int it = 0; it < n_rounds; ++it) {
         const int round = first_round + it;
         const int par = round & 1;
@@ -113,9 +126,13 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
             if (rc) return rc;
         }
         if (plan->decoder) {
-            int rc = eh_decoder_round(plan->decoder, round, r0 + it, stream);
+            int rc = eh_decoder_round(plan->decoder, round, r0 + it, (void*)dec_stream);
             if (rc) return rc;
         }
+    }
+    if (forked) {
+        EH_CUDA(cudaEventRecord((cudaEvent_t)plan->ev_join, dec_stream));
+        EH_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)plan->ev_join, 0));
     }
     return EH_OK;
 }

@@ -190,11 +190,7 @@ static int launch_tc(const CUtensorMap& mx, const CUtensorMap& mb, const TcParam
     constexpr size_t smem = 1024 + (size_t)TC_STAGES * (TC_A_BYTES + BN * TC_BK * 4) + 256;
     static_assert(128 * (BN + 1) * 4 <= TC_STAGES * (TC_A_BYTES + BN * TC_BK * 4), "reduction scratch fits the ring");
     auto kern = eval_tc_kernel<NB>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), (int)smem);
     const long long n_tiles = (p.rows + TC_BM - 1) / TC_BM;
     long long grid = dev_info().sm_count;
     if (grid > n_tiles) grid = n_tiles;

@@ -20,6 +20,7 @@
 // The kernel starts prefetching X while it still waits for this round's parameters
 // (`d_beta_flag`), i.e. the parameter broadcast overlaps the first tiles of the next round.
 #include <stdlib.h>
+#include <atomic>
 
 #include "grad_dense.cuh"
 
@@ -260,12 +261,8 @@ static int launch(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStre
     p.n_stages = stages;
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
     auto kern = grad_dense_kernel<E, DV, RB>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
-        attr_done = true;
-    }
-    const int grid = assign_ctas(p, di.sm_count);
+    EH_SET_MAX_SMEM((kern), GD_SMEM_BUDGET);
+    const int grid = assign_ctas(p, worker_sms());
     p.ldp = p.ld;
     const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.ldp * sizeof(float);
     EH_REQUIRE(scratch_bytes >= need, "grad_dense: scratch too small (%zu < %zu)", scratch_bytes, need);
@@ -407,7 +404,11 @@ extern "C" int eh_grad_dense_multi(const eh_grad_job* jobs, int n_jobs, void* d_
 //
 // Set-up: the first call on each device resolves the array's device address with
 // cudaGetSymbolAddress (in host code the array's name is only a host-side stand-in, not a device
-// address) and caches it per device.  Make that first call before any stream capture begins.
+// address) and caches it per device.  Make that first call before any stream capture begins, and
+// make it at start-up, while device memory is still available: it is also the moment the CUDA
+// runtime loads this library's module onto that device (which is when the driver places the
+// 2.5 MiB array and the kernel code) and when the kernel's shared-memory attribute is set, so a
+// process that has already committed every byte of HBM can fail right there -- never later.
 // Every call shares the one array, which still holds the previous call's partials: the barrier
 // words that must start at zero are cleared on the caller's stream before each launch, the
 // partials are fully overwritten before they are read.  Two calls that overlap on the GPU
@@ -434,14 +435,17 @@ extern "C" int eh_grad_dense_noalloc(const eh_grad_job* j, void* stream) {
                "grad_dense_noalloc: device has %d SMs, built-in scratch is sized for %d CTAs", di.sm_count,
                EH_NOALLOC_MAX_CTAS);
     // once per device, with that device current: device address of the file-scope array
-    static void* dev_ptr[64] = {nullptr};
-    if (dev_ptr[di.device] == nullptr) {
+    // (atomic: two host threads on different devices may both be in their first call; the value written is
+    // the same for a given device, so a lost race only repeats the lookup)
+    static std::atomic<void*> dev_ptr[64];
+    void* scratch = dev_ptr[di.device].load(std::memory_order_acquire);
+    if (scratch == nullptr) {
         void* p = nullptr;
         EH_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
         EH_REQUIRE(p != nullptr, "grad_dense_noalloc: cudaGetSymbolAddress returned a null address");
-        dev_ptr[di.device] = p;
+        dev_ptr[di.device].store(p, std::memory_order_release);
+        scratch = p;
     }
-    void* scratch = dev_ptr[di.device];
     // the array keeps the last call's contents: zero the barrier/decision words, stream-ordered
     EH_CUDA(cudaMemsetAsync(scratch, 0, sizeof(GradScratchHdr), (cudaStream_t)stream));
     return eh_grad_dense(j, scratch, EH_NOALLOC_BYTES, stream);

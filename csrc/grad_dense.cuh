@@ -132,6 +132,8 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
             // last CTA: every CTA is past the barrier wait -> safe to recycle the counters
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_arrival_time(p.job_flag[j]);
             __threadfence_system();
             for (int j = 0; j < p.n_jobs; ++j)
                 if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);      // ordered by the fence above

@@ -269,6 +269,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_cluster_kernel(const
         if (old == (uint32_t)G - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            if (p.flag) st_arrival_time(p.flag);
             __threadfence_system();
             if (p.flag) st_relaxed_sys(p.flag, p.stamp);
         }
@@ -300,11 +301,7 @@ static int launch_cluster_t(GradParams& p, void* d_scratch, size_t scratch_bytes
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
     const long long n_steps = (long long)p.steps_per_seg * p.n_segs;
     auto kern = grad_dense_cluster_kernel<DV, RB>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), GD_SMEM_BUDGET);
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cudaLaunchAttribute attrs[1];
@@ -317,7 +314,7 @@ static int launch_cluster_t(GradParams& p, void* d_scratch, size_t scratch_bytes
     cfg.blockDim = dim3(GD_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cfg.gridDim = dim3(dev_info().sm_count / CS * CS);
+    cfg.gridDim = dim3(worker_sms() / CS * CS);
     int max_clusters = 0;
     EH_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
     EH_REQUIRE(max_clusters >= 1, "grad_dense(cluster): no cluster of %d CTAs fits on this device", CS);

@@ -228,12 +228,8 @@ static int launch_rw(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaS
     p.n_stages = stages;
     p.steps_per_seg = (p.rows_per_seg + RB - 1) / RB;
     auto kern = grad_dense_rowwarp_kernel<E, LPR, DVW>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GD_SMEM_BUDGET));
-        attr_done = true;
-    }
-    const int grid = assign_ctas(p, di.sm_count);
+    EH_SET_MAX_SMEM((kern), GD_SMEM_BUDGET);
+    const int grid = assign_ctas(p, worker_sms());
     p.ldp = p.ld;
     const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.ldp * sizeof(float);
     EH_REQUIRE(scratch_bytes >= need, "grad_dense: scratch too small (%zu < %zu)", scratch_bytes, need);

@@ -75,7 +75,10 @@ __global__ void wide_ship_kernel(const float* __restrict__ g, float* __restrict_
     __threadfence_system();
 }
 __global__ void wide_flag_kernel(uint32_t* flag, uint32_t stamp, const uint32_t* skip) {
-    if (threadIdx.x == 0 && blockIdx.x == 0 && !(skip && *skip)) st_release_sys(flag, stamp);
+    if (threadIdx.x == 0 && blockIdx.x == 0 && !(skip && *skip)) {
+        st_arrival_time(flag);
+        st_release_sys(flag, stamp);
+    }
 }
 
 int launch_wide(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream_t st) {
@@ -91,7 +94,7 @@ int launch_wide(GradParams& p, void* d_scratch, size_t scratch_bytes, cudaStream
         skp = skip;
     }
     EH_CUDA(cudaMemsetAsync(g, 0, (size_t)p.ld * sizeof(float), st));
-    const int sm = dev_info().sm_count;
+    const int sm = worker_sms();
     for (int sg = 0; sg < p.n_segs; ++sg) {
         for (int r0 = 0; r0 < p.rows_per_seg; r0 += WIDE_CHUNK) {
             const int rows = (p.rows_per_seg - r0) < WIDE_CHUNK ? (p.rows_per_seg - r0) : WIDE_CHUNK;

@@ -154,6 +154,7 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
         if (old == gridDim.x - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            if (p.flag) st_arrival_time(p.flag);
             __threadfence_system();
             if (p.flag) st_release_sys(p.flag, p.stamp);
         }
@@ -302,6 +303,8 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
         if (old == (uint32_t)G - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_arrival_time(p.job_flag[j]);
             __threadfence_system();
             for (int j = 0; j < p.n_jobs; ++j)
                 if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);       // ordered by the fence above
@@ -381,7 +384,7 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
         const size_t smem = both ? 2 * acc_bytes : acc_bytes;
         // CTAs per message in proportion to its rows (32 rows of work per warp at least), every message >= 1
         const long long total_rows = (long long)j->rows_per_seg * nseg;
-        long long grid = di.sm_count;
+        long long grid = worker_sms();
         const long long want = (total_rows * 32 + GES_THREADS - 1) / GES_THREADS;
         if (grid > want) grid = want;
         if (grid < n_jobs) grid = n_jobs;
@@ -397,11 +400,8 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
         EH_REQUIRE(scratch_bytes >= sizeof(EllScratchHdr) + (size_t)grid * j->d * sizeof(float),
                    "grad_ell: scratch too small for the shared-memory variant");
         const void* kern = both ? (const void*)grad_ell_smem_kernel<true> : (const void*)grad_ell_smem_kernel<false>;
-        static bool attr_done[2] = {false, false};
-        if (!attr_done[both]) {
-            EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GES_SMEM_LIMIT));
-            attr_done[both] = true;
-        }
+        if (both) { EH_SET_MAX_SMEM((grad_ell_smem_kernel<true>), (int)GES_SMEM_LIMIT); }
+        else { EH_SET_MAX_SMEM((grad_ell_smem_kernel<false>), (int)GES_SMEM_LIMIT); }
         void* args[] = {(void*)&p, (void*)&partials};
         return launch_grid_sync(kern, dim3((unsigned)grid), dim3(GES_THREADS), args, smem, (cudaStream_t)stream);
     }
@@ -412,7 +412,7 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
     long long want = (p.rows * 32 + GE_THREADS - 1) / GE_THREADS;      // one warp per row
     long long cols = ((long long)j->d + GE_THREADS - 1) / GE_THREADS;
     if (cols > want) want = cols;
-    long long grid = (long long)di.sm_count * occ;
+    long long grid = (long long)worker_sms() * occ;
     if (grid > want) grid = want;
     if (grid < 1) grid = 1;
     void* args[] = {(void*)&p};

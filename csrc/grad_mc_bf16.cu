@@ -413,6 +413,7 @@ mc_bf16_kernel(const __grid_constant__ McBf16Maps maps, const McBf16Params p) {
         if (old == (uint32_t)G - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            if (p.flag) st_arrival_time(p.flag);
             __threadfence_system();
             if (p.flag) st_relaxed_sys(p.flag, p.stamp);
         }
@@ -456,11 +457,7 @@ template <int NB, bool SPLIT>
 static int launch_mc_bf16(const McBf16Maps& maps, McBf16Params& p, int grid, cudaStream_t st) {
     const size_t smem = mc_bf16_smem(p.dk, 16 * NB, p.n_stages);
     auto kern = mc_bf16_kernel<NB, SPLIT>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), 227 * 1024);
     void* args[] = {(void*)&maps, (void*)&p};
     return launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(MB_THREADS), args, smem, st);
 }
@@ -492,7 +489,7 @@ int mc_bf16_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes, 
     p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     const long long n_tiles = (long long)p.n_segs * p.tiles_per_seg;
-    long long grid = dev_info().sm_count;
+    long long grid = worker_sms();
     if (grid > n_tiles) grid = n_tiles;
     const size_t need = sizeof(GradScratchHdr) + (size_t)grid * p.out_rows * p.ldw * sizeof(float);
     EH_REQUIRE(fused_bytes >= need, "grad_mc(bf16): scratch too small (%zu < %zu)", fused_bytes, need);

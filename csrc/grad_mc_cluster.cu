@@ -435,6 +435,7 @@ mc_cluster_kernel(const __grid_constant__ Mc2Maps maps, const Mc2Params p) {
         if (old == (uint32_t)G - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            if (p.flag) st_arrival_time(p.flag);
             __threadfence_system();
             if (p.flag) st_relaxed_sys(p.flag, p.stamp);
         }
@@ -484,11 +485,7 @@ static int launch_mc2(const Mc2Maps& maps, Mc2Params& p, void* fused_scratch, si
     const int CN = 8 * NBC;
     const size_t smem = mc2_smem(CN, p.npc, p.n_stages);
     auto kern = mc_cluster_kernel<NBC>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), 227 * 1024);
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cudaLaunchAttribute attrs[1];
@@ -501,7 +498,7 @@ static int launch_mc2(const Mc2Maps& maps, Mc2Params& p, void* fused_scratch, si
     cfg.blockDim = dim3(MC2_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cfg.gridDim = dim3(dev_info().sm_count / p.CS * p.CS);
+    cfg.gridDim = dim3(worker_sms() / p.CS * p.CS);
     int max_clusters = 0;
     EH_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
     EH_REQUIRE(max_clusters >= 1, "grad_mc: no cluster of %d CTAs fits on this device", p.CS);

@@ -355,6 +355,7 @@ mc_fused_kernel(const __grid_constant__ McFusedMaps maps, const McFusedParams p)
         if (old == (uint32_t)G - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
+            if (p.flag) st_arrival_time(p.flag);
             __threadfence_system();
             if (p.flag) st_relaxed_sys(p.flag, p.stamp);
         }
@@ -386,11 +387,7 @@ template <int NBC>
 static int launch_fused(const McFusedMaps& maps, McFusedParams& p, int grid, cudaStream_t st) {
     const size_t smem = mc_fused_smem(p.dk, 8 * NBC, p.n_stages, p.n_rbuf);
     auto kern = mc_fused_kernel<NBC>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), 227 * 1024);
     void* args[] = {(void*)&maps, (void*)&p};
     return launch_grid_sync((const void*)kern, dim3((unsigned)grid), dim3(MF_THREADS), args, smem, st);
 }
@@ -425,7 +422,7 @@ int mc_fused_launch(const eh_mc_job* j, void* fused_scratch, size_t fused_bytes,
     p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     const long long n_tiles = (long long)p.n_segs * p.tiles_per_seg;
-    long long grid = dev_info().sm_count;
+    long long grid = worker_sms();
     if (grid > n_tiles) grid = n_tiles;
     const size_t need = sizeof(GradScratchHdr) + (size_t)grid * CN * p.ldw * sizeof(float);
     EH_REQUIRE(fused_bytes >= need, "grad_mc: scratch too small for the one-pass kernel (%zu < %zu)", fused_bytes, need);

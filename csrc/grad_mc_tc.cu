@@ -313,20 +313,19 @@ __global__ void mc_ship_kernel(const float* __restrict__ g, float* __restrict__ 
     __threadfence_system();
 }
 __global__ void mc_flag_kernel(uint32_t* flag, uint32_t stamp, const uint32_t* skip) {
-    if (threadIdx.x == 0 && blockIdx.x == 0 && !(skip && *skip)) st_release_sys(flag, stamp);
+    if (threadIdx.x == 0 && blockIdx.x == 0 && !(skip && *skip)) {
+        st_arrival_time(flag);
+        st_release_sys(flag, stamp);
+    }
 }
 
 template <int NB>
 static int launch_fwd(const CUtensorMap& mx, const CUtensorMap& mw, const McFwdParams& p, cudaStream_t st) {
     constexpr size_t smem = 1024 + (size_t)MC_STAGES * (TC_A_BYTES + 16 * NB * TC_BK * 4) + 256;
     auto kern = mc_forward_kernel<NB>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), (int)smem);
     const long long n_tiles = (p.rows + TC_BM - 1) / TC_BM;
-    long long grid = dev_info().sm_count;
+    long long grid = worker_sms();
     if (grid > n_tiles) grid = n_tiles;
     kern<<<(unsigned)grid, TC_THREADS, smem, st>>>(mx, mw, p);
     EH_CUDA(cudaGetLastError());
@@ -337,13 +336,9 @@ template <int NB>
 static int launch_bwd(const CUtensorMap& mx, const CUtensorMap& mr, const McBwdParams& p, cudaStream_t st) {
     constexpr size_t smem = 1024 + (size_t)MC_STAGES * (MCB_A_BYTES + 16 * NB * MCB_KR * 4) + 256;
     auto kern = mc_backward_kernel<NB>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        EH_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-    }
+    EH_SET_MAX_SMEM((kern), (int)smem);
     const long long n_ksteps = (p.rows + MCB_KR - 1) / MCB_KR;
-    long long grid = dev_info().sm_count;
+    long long grid = worker_sms();
     if (grid > n_ksteps) grid = n_ksteps;
     kern<<<(unsigned)grid, TC_THREADS, smem, st>>>(mx, mr, p);
     EH_CUDA(cudaGetLastError());

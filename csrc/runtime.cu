@@ -5,6 +5,7 @@
 // every worker GPU stores into directly over NVLink; the per-round `Isend(beta)` loop
 // (naive.py:97-98) becomes peer stores into each GPU's `beta[2][d]` buffer.
 #include <stdarg.h>
+#include <atomic>
 #include <stdlib.h>
 
 #include "workspace.cuh"
@@ -39,11 +40,19 @@ const DevInfo& dev_info() {
     return di;
 }
 
+static std::atomic<int> g_reserved_sms[64];
+
+int worker_sms() {
+    const DevInfo& di = dev_info();
+    if (di.device < 0) return 0;
+    const int left = di.sm_count - g_reserved_sms[di.device].load(std::memory_order_relaxed);
+    return left < 1 ? 1 : left;
+}
+
 uint32_t next_launch_seq() {
-    static uint32_t seq = 1;
-    const uint32_t v = seq++;
-    if (seq >= (1u << 30)) seq = 1;
-    return v;
+    // 1 .. 2^30-1, wraps; atomic so that host threads driving different devices can share it
+    static std::atomic<uint32_t> seq{0};
+    return (seq.fetch_add(1u, std::memory_order_relaxed) % ((1u << 30) - 1u)) + 1u;
 }
 
 int launch_grid_sync(const void* kern, dim3 grid, dim3 block, void** args, size_t smem, cudaStream_t stream) {
@@ -76,6 +85,83 @@ extern "C" int eh_device_info(int* sm_count, int* grad_dense_ctas, int* decoder_
     if (sm_count) *sm_count = di.sm_count;
     if (grad_dense_ctas) *grad_dense_ctas = di.sm_count;
     if (decoder_ctas) *decoder_ctas = di.sm_count;
+    return EH_OK;
+}
+
+extern "C" int eh_set_reserved_sms(int n) {
+    const eh::DevInfo& di = eh::dev_info();
+    EH_REQUIRE(di.device >= 0, "no CUDA device");
+    EH_REQUIRE(n >= 0 && n < di.sm_count, "reserved SMs (%d) must be in 0..%d", n, di.sm_count - 1);
+    eh::g_reserved_sms[di.device].store(n, std::memory_order_relaxed);
+    return EH_OK;
+}
+
+extern "C" int eh_worker_sms(void) { return eh::worker_sms(); }
+
+// ------------------------------------------------------------------------------------------
+// Clock alignment.  %globaltimer is a per-GPU counter; message completion times stamped on a
+// worker GPU are compared with the decoder GPU's own clock, so the offset of every peer is
+// measured once at set-up by a ping-pong through the peer-mapped control words: the root stores
+// seq into the peer's CTL_PING, the peer answers with its clock + seq in the root's CTL_PONG;
+// offset = t_peer - (t_send + t_recv) / 2 of the exchange with the smallest round trip.
+// ------------------------------------------------------------------------------------------
+namespace eh {
+__global__ void clock_sync_root_kernel(CtlWord* peer_ctl, CtlWord* my_ctl, uint32_t base, int iters,
+                                       long long* out_offset, long long* out_rtt, unsigned long long timeout_ns) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    long long best_rtt = -1, best_off = 0;
+    for (int k = 1; k <= iters; ++k) {
+        const uint32_t seq = base + (uint32_t)k;
+        const uint64_t t0 = globaltimer();
+        st_release_sys(&peer_ctl[CTL_PING].v, seq);
+        bool ok = true;
+        while (ld_acquire_sys(&my_ctl[CTL_PONG].v) != seq) {
+            if (globaltimer() - t0 > timeout_ns) { ok = false; break; }
+        }
+        if (!ok) break;
+        const uint64_t t1 = globaltimer();
+        const uint64_t tp = ld_arrival_time(&my_ctl[CTL_PONG].v);
+        const long long rtt = (long long)(t1 - t0);
+        if (best_rtt < 0 || rtt < best_rtt) {
+            best_rtt = rtt;
+            best_off = (long long)tp - (long long)(t0 + (t1 - t0) / 2);
+        }
+    }
+    *out_offset = best_off;
+    *out_rtt = best_rtt;
+}
+__global__ void clock_sync_peer_kernel(CtlWord* my_ctl, CtlWord* root_ctl, uint32_t base, int iters,
+                                       unsigned long long timeout_ns) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const uint64_t t_begin = globaltimer();
+    for (int k = 1; k <= iters; ++k) {
+        const uint32_t seq = base + (uint32_t)k;
+        while (ld_acquire_sys(&my_ctl[CTL_PING].v) != seq) {
+            if (globaltimer() - t_begin > timeout_ns) return;
+        }
+        st_arrival_time(&root_ctl[CTL_PONG].v);
+        st_release_sys(&root_ctl[CTL_PONG].v, seq);
+    }
+}
+}  // namespace eh
+
+extern "C" int eh_clock_sync_root(const eh_ws_layout* lay, void* d_ws_local, void* d_ws_peer, uint32_t base, int iters,
+                                  long long* d_offset_ns, long long* d_rtt_ns, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws_local && d_ws_peer && d_offset_ns && d_rtt_ns && iters >= 1, "clock_sync_root: bad argument");
+    clock_sync_root_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ws_ctl(d_ws_peer, *lay), ws_ctl(d_ws_local, *lay), base, iters,
+                                                             d_offset_ns, d_rtt_ns, 20ull * 1000000000ull);
+    EH_CUDA(cudaGetLastError());
+    return EH_OK;
+}
+
+extern "C" int eh_clock_sync_peer(const eh_ws_layout* lay, void* d_ws_local, void* d_ws_root, uint32_t base, int iters,
+                                  void* stream) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws_local && d_ws_root && iters >= 1, "clock_sync_peer: bad argument");
+    clock_sync_peer_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ws_ctl(d_ws_local, *lay), ws_ctl(d_ws_root, *lay), base, iters,
+                                                             60ull * 1000000000ull);
+    EH_CUDA(cudaGetLastError());
     return EH_OK;
 }
 

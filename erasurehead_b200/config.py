@@ -105,6 +105,9 @@ class RunConfig:
     cuda_graph: bool = False               # capture each enqueue of rounds into one CUDA graph
     beta_push: str = "p2p"                 # parameter broadcast: p2p (peer stores) | multicast (NVLS multimem.st)
     dtype: str = "fp32"                    # storage of dense features on the GPU: fp32 | bf16 (half the HBM traffic)
+    decoder: str = "concurrent"            # concurrent: the decoder runs on its own high-priority stream on SMs the
+                                           # gradient kernels leave free (a round costs max(compute, wait));
+                                           # inline: after the root's gradient kernels on one stream (compute + wait)
     debug_poison: bool = False             # fill every message slot with NaN before a run (stale-read detector)
 
     def __post_init__(self):

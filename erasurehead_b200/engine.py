@@ -132,6 +132,13 @@ class Engine:
         d = cfg.n_cols
         self.ws = Workspace(ctx, spec.n, spec.n_msgs, self.d_eff)
         lay = self.ws.lay
+        if cfg.decoder not in ("concurrent", "inline"):
+            raise ValueError("decoder must be concurrent or inline")
+        # worker kernels stamp completion with their own GPU's clock: align the clocks once
+        self.ws.sync_clocks()
+        # the decoder's SMs: the root's gradient kernels leave them free (no effect on other ranks)
+        self.dec_ctas = int(L.eh_decoder_ctas(int(lay.d_pad))) if cfg.decoder == "concurrent" else 0
+        _lib.check(L.eh_set_reserved_sms(self.dec_ctas if ctx.is_root else 0), "eh_set_reserved_sms")
         # ---- partitions resident on this GPU (deduplicated across local workers)
         self.parts: Dict[int, tuple] = {}
         mine = ctx.local_workers(spec.n)
@@ -206,6 +213,17 @@ class Engine:
         plan.decoder = C.pointer(self.dec) if self.dec is not None else None
         plan.timeout_ns = self.timeout_ns
         plan.lay = lay
+        self._dec_stream = None
+        if self.dec is not None and cfg.decoder == "concurrent":
+            lo, hi = torch.cuda.Stream.priority_range()          # (least, greatest) = (0, -N)
+            self._dec_stream = torch.cuda.Stream(device=dev, priority=hi)
+            self._ev_fork = torch.cuda.Event(enable_timing=False)
+            self._ev_join = torch.cuda.Event(enable_timing=False)
+            # the events are created lazily by torch: record once so that the handles exist
+            self._ev_fork.record()
+            self._ev_join.record()
+            plan.dec_stream = self._dec_stream.cuda_stream
+            plan.ev_fork, plan.ev_join = self._ev_fork.cuda_event, self._ev_join.cuda_event
         self.plan = plan
 
     def _device_partition(self, p: int):
@@ -265,6 +283,9 @@ class Engine:
         self.t_weights = torch.zeros((R, n), dtype=torch.float64, device=dev)
         self.t_ncol = torch.zeros(R, dtype=torch.int32, device=dev)
         self.t_tstart = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.t_done = torch.full((R, n), -1.0, dtype=torch.float64, device=dev)
+        off = [self.ws.clock_offset_ns[self.ctx.owner(w)] for w in range(n)]
+        self.t_clock_off = t(np.asarray(off, dtype=np.int64), torch.int64)
         self.t_decscratch = torch.zeros((_lib.lib().eh_decoder_scratch_bytes() + 7) // 8, dtype=torch.int64, device=dev)
         D = _lib.DecoderDesc()
         D.n_workers, D.n_msgs, D.n_groups, D.s = n, spec.n_msgs, spec.n_groups, spec.s
@@ -290,6 +311,9 @@ class Engine:
         D.alpha, D.n_rows, D.lr_scale = float(cfg.alpha), float(cfg.n_rows), float(spec.lr_scale)
         D.timeout_ns = self.timeout_ns
         D.lay = self.ws.lay
+        D.d_clock_off = self.t_clock_off.data_ptr() if self.ctx.world > 1 else None
+        D.d_done = self.t_done.data_ptr()
+        D.dec_ctas = self.dec_ctas
         self.dec = D
 
     # ------------------------------------------------------------------ running
@@ -479,7 +503,8 @@ class Engine:
             betaset, u, beta = unpack_mc(betaset, dd, cc), unpack_mc(u, dd, cc), unpack_mc(beta, dd, cc)
         return oracle.RunResult(
             betaset=betaset, timeset=cpu(self.t_timeset), worker_timeset=cpu(self.t_wts),
-            weights=cpu(self.t_weights), n_collected=cpu(self.t_ncol).astype(np.int64), u=u, beta=beta)
+            weights=cpu(self.t_weights), n_collected=cpu(self.t_ncol).astype(np.int64), u=u, beta=beta,
+            done=cpu(self.t_done))
 
     # ------------------------------------------------------------------ evaluation
     def evaluate(self, res: Optional[oracle.RunResult] = None):

@@ -88,14 +88,16 @@ class DecoderDesc(C.Structure):
                 ("d_weights", C.c_void_p), ("d_ncollected", C.c_void_p), ("d_tstart", C.c_void_p),
                 ("d_scratch", C.c_void_p), ("d_beta_mc", C.c_void_p),
                 ("alpha", C.c_double), ("n_rows", C.c_double), ("lr_scale", C.c_double),
-                ("timeout_ns", C.c_uint64), ("lay", WsLayout)]
+                ("timeout_ns", C.c_uint64), ("lay", WsLayout),
+                ("d_clock_off", C.c_void_p), ("d_done", C.c_void_p), ("dec_ctas", C.c_int32), ("reserved", C.c_int32)]
 
 
 class RoundPlan(C.Structure):
     _fields_ = [("n_jobs", C.c_int32), ("reserved", C.c_int32), ("jobs", C.POINTER(WorkerJob)),
                 ("d_ws_local", C.c_void_p), ("d_ws_root", C.c_void_p), ("d_scratch", C.c_void_p),
                 ("d_beta_local", C.c_void_p), ("scratch_bytes", C.c_size_t), ("decoder", C.POINTER(DecoderDesc)),
-                ("timeout_ns", C.c_uint64), ("lay", WsLayout)]
+                ("timeout_ns", C.c_uint64), ("lay", WsLayout),
+                ("dec_stream", C.c_void_p), ("ev_fork", C.c_void_p), ("ev_join", C.c_void_p)]
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -138,6 +140,11 @@ def _declare(lib):
         "eh_grad_ell": (i32, [P(GradEllJob), vp, sz, vp]),
         "eh_grad_ell_multi": (i32, [P(GradEllJob), i32, vp, sz, vp]),
         "eh_decoder_scratch_bytes": (sz, []),
+        "eh_decoder_ctas": (i32, [i32]),
+        "eh_set_reserved_sms": (i32, [i32]),
+        "eh_worker_sms": (i32, []),
+        "eh_clock_sync_root": (i32, [P(WsLayout), vp, vp, C.c_uint32, i32, vp, vp, vp]),
+        "eh_clock_sync_peer": (i32, [P(WsLayout), vp, vp, C.c_uint32, i32, vp]),
         "eh_decoder_round": (i32, [P(DecoderDesc), i32, i32, vp]),
         "eh_decoder_publish": (i32, [P(DecoderDesc), i32, vp]),
         "eh_run_rounds": (i32, [P(RoundPlan), i32, i32, i32, vp]),
@@ -168,8 +175,13 @@ def lib():
     global _lib
     with _lock:
         if _lib is None:
-            if not os.path.exists(LIB_PATH):
+            # build() is a no-op when the library is newer than every source and header, so a stale
+            # binary is never loaded against newer structs; a box without nvcc keeps what it has
+            try:
                 build()
+            except (EhError, OSError):
+                if not os.path.exists(LIB_PATH):
+                    raise
             _lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
             _declare(_lib)
     return _lib

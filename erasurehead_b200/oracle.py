@@ -35,6 +35,8 @@ class RunResult:
     u: Optional[np.ndarray] = None      # AGD auxiliary state after the last round
     beta: Optional[np.ndarray] = None   # parameters after the last round
     wall_time: float = 0.0
+    done: Optional[np.ndarray] = None   # [R, n] seconds from round start to completion of w's coded message
+                                        # (before the injected delay); GPU engine only, -1 if never seen
 
 
 def gd_update(beta, g, eta, alpha, grad_mult):
@@ -103,6 +105,7 @@ def plan_round(spec: SchemeSpec, delay_row: np.ndarray, compute_time: float = 0.
     n_priv = n_coded = 0
     t_last = 0.0
     seen_t = np.full(n, -1.0)
+    order = []
     for (t, _, w, kind) in events:
         if spec.stop(n_priv, n_coded, int(grp_cov.sum())):
             break
@@ -117,6 +120,7 @@ def plan_round(spec: SchemeSpec, delay_row: np.ndarray, compute_time: float = 0.
             continue
         n_coded += 1
         done[w] = True
+        order.append(w)
         gid = spec.group_of[w]
         if not grp_cov[gid]:
             grp_cov[gid] = True
@@ -128,7 +132,13 @@ def plan_round(spec: SchemeSpec, delay_row: np.ndarray, compute_time: float = 0.
     elif spec.decode == DECODE_FIRST_PER_GROUP:
         a = first_of_group.astype(np.float64)
     else:
-        a = codes.decode_weights(spec.B, done)                             # coded.py:147-149
+        # coded.py:147-149.  partial_coded can collect more than n-s coded messages while it waits for the
+        # private parts (partial_coded.py:174); the reference then takes the minimum-norm least-squares row
+        # over all of them, this framework (device and oracle alike) the exact row of the FIRST n-s arrivals.
+        # Both satisfy a.B[done] = 1, so the decoded gradient is the same; only the weights differ.
+        sel = np.zeros(n, dtype=bool)
+        sel[order[:max(1, spec.n - spec.s)]] = True
+        a = codes.decode_weights(spec.B, sel)
     wt = np.where(done, seen_t, -1.0)                                      # -1 for the uncollected
     return a, priv, t_last, n_coded, wt
 

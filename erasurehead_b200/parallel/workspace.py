@@ -52,6 +52,39 @@ class Workspace:
                 self.peers[r] = p.value
                 self._opened.append(p.value)
         self.root = self.peers[0]
+        self.clock_offset_ns: List[int] = [0] * ctx.world      # peer clock - root clock (root only)
+        self.clock_rtt_ns: List[int] = [0] * ctx.world
+
+    def sync_clocks(self, iters: int = 64) -> None:
+        """Measure every peer GPU's ``%globaltimer`` offset against the root's (one ping-pong kernel
+        pair per peer through the control words).  Worker kernels stamp message completion with
+        their own GPU's clock; the decoder subtracts these offsets to put the stamps on its clock."""
+        import torch
+        ctx, L = self.ctx, lib()
+        if ctx.world == 1:
+            return
+        self.reset()
+        torch.cuda.synchronize()
+        ctx.barrier()
+        if ctx.is_root:
+            out = torch.zeros(2 * ctx.world, dtype=torch.int64, device=ctx.device)
+            for r in range(1, ctx.world):
+                check(L.eh_clock_sync_root(C.byref(self.lay), self.local, self.peers[r], r << 16, iters,
+                                           out.data_ptr() + 8 * r, out.data_ptr() + 8 * (ctx.world + r), stream_ptr()),
+                      "eh_clock_sync_root")
+            torch.cuda.synchronize()
+            v = out.cpu().tolist()
+            self.clock_offset_ns = [int(x) for x in v[:ctx.world]]
+            self.clock_rtt_ns = [int(x) for x in v[ctx.world:]]
+            if any(x < 0 for x in self.clock_rtt_ns[1:]):
+                raise RuntimeError(f"clock alignment with a peer GPU timed out (round trips {self.clock_rtt_ns})")
+        else:
+            check(L.eh_clock_sync_peer(C.byref(self.lay), self.local, self.root, ctx.rank << 16, iters, stream_ptr()),
+                  "eh_clock_sync_peer")
+            torch.cuda.synchronize()
+        ctx.barrier()
+        self.reset()
+        torch.cuda.synchronize()
 
     def reset(self) -> None:
         check(lib().eh_ws_reset(C.byref(self.lay), self.local, stream_ptr()), "eh_ws_reset")

@@ -80,7 +80,10 @@ int eh_ws_error(const eh_ws_layout* lay, void* d_ws, int* err, void* stream);
  * combined through `d_scratch` (>= eh_grad_dense_scratch_bytes) by a device-wide barrier and
  * the result is written to `d_out` (local or peer memory).  If `d_flag` is non-NULL the kernel
  * first waits for the parameter flag (`d_beta_flag`, value >= stamp) and, once `d_out` is
- * complete, publishes `stamp` to `d_flag` with release/system semantics.
+ * complete, publishes `stamp` to `d_flag` with release/system semantics.  `d_flag` addresses a
+ * 16-byte ARRIVAL RECORD (8-byte aligned; 128 bytes apart in the workspace): word 0 receives the
+ * stamp, bytes 8..15 the publishing GPU's %globaltimer at completion -- every gradient entry point
+ * below follows this contract.
  * ---------------------------------------------------------------------------------------- */
 #define EH_MAX_SEGS 16
 
@@ -115,9 +118,10 @@ int eh_grad_dense_multi(const eh_grad_job* jobs, int n_jobs, void* d_scratch, si
  * allocator): the scratch lives in a file-scope device array inside the library (2.5 MiB per
  * GPU, held until exit).  No counterpart in the reference.  Limits: ld <= 4096 floats
  * (eh_grad_dense_noalloc_max_ld()), devices with <= 160 SMs; larger shapes return EH_EINVAL.
- * The first call on each device resolves the array's address (make it before any stream
- * capture); calls sharing a device must be stream-ordered -- overlapping calls race on the array.
- * Calls no cudaMalloc/cudaFree and no allocating library routine. */
+ * The first call on each device resolves the array's address and triggers the runtime's one-time
+ * module load for that device (make it at start-up, before memory is fully committed and before
+ * any stream capture); calls sharing a device must be stream-ordered -- overlapping calls race on
+ * the array.  The entry point itself calls no cudaMalloc/cudaFree and no allocating library routine. */
 size_t eh_grad_dense_noalloc_max_ld(void);
 int eh_grad_dense_noalloc(const eh_grad_job* job, void* stream);
 
@@ -225,9 +229,27 @@ typedef struct eh_decoder_desc {
     double   alpha, n_rows, lr_scale;
     uint64_t timeout_ns;            /* watchdog for one round (0 = 60 s) */
     eh_ws_layout lay;
+    const int64_t* d_clock_off;     /* [n_workers] clock of the GPU hosting worker w minus this GPU's clock, ns
+                                       (eh_clock_sync_root); NULL = one clock */
+    double*  d_done;                /* optional output [rounds, n_workers]: seconds from round start to the
+                                       completion stamp of w's coded message (before the injected delay) */
+    int32_t  dec_ctas;              /* grid size cap (0 = one CTA per SM); eh_decoder_ctas(d_pad) when the decoder
+                                       runs next to gradient kernels that leave that many SMs free */
+    int32_t  reserved;
 } eh_decoder_desc;
 
 size_t eh_decoder_scratch_bytes(void);
+int eh_decoder_ctas(int d_pad);
+/* SMs of the current device that gradient kernels leave free (for a concurrent decoder). */
+int eh_set_reserved_sms(int n);
+int eh_worker_sms(void);
+/* Clock alignment between the root GPU and one peer (run both sides concurrently, root on the
+ * root's stream, peer on the peer's; `base` distinguishes exchanges).  Results (device scalars on
+ * the root): peer clock minus root clock and the best round trip, in ns. */
+int eh_clock_sync_root(const eh_ws_layout* lay, void* d_ws_local, void* d_ws_peer, uint32_t base, int iters,
+                       long long* d_offset_ns, long long* d_rtt_ns, void* stream);
+int eh_clock_sync_peer(const eh_ws_layout* lay, void* d_ws_local, void* d_ws_root, uint32_t base, int iters,
+                       void* stream);
 /* round = global round index (AGD's theta uses it); r = index into the per-round tables. */
 int eh_decoder_round(const eh_decoder_desc* desc, int round, int r, void* stream);
 /* Publish beta_0 (from d_beta64) to every peer and open round `round` (flag = round+1). */
@@ -266,6 +288,12 @@ typedef struct eh_round_plan {
     const eh_decoder_desc* decoder;  /* non-NULL on the root rank only */
     uint64_t timeout_ns;
     eh_ws_layout lay;
+    void*    dec_stream;             /* optional (root): stream of the decoder kernels.  When set and different
+                                        from `stream`, the decoder of round i runs CONCURRENTLY with the gradient
+                                        kernels of round i of this GPU (fork/join by events inside eh_run_rounds);
+                                        call eh_set_reserved_sms(desc.dec_ctas) first so that it always finds SMs */
+    void*    ev_fork;                /* cudaEvent_t pair owned by the caller (cudaEventDisableTiming) */
+    void*    ev_join;
 } eh_round_plan;
 
 /* r0 = index of `first_round` in the decoder's per-round tables. */

@@ -367,3 +367,30 @@ def test_predict_margins_on_gpu_uses_tensor_core_path():
     P = predict.margins(X, B)
     assert (P.double() - X.double() @ B.double().t()).abs().max().item() < 5e-3
     assert predict.predict_proba(X, B[0]).shape == (500,)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_kernels_on_a_second_device_in_one_process():
+    """Per-device kernel attributes (dynamic shared memory) and the per-device scratch address of the
+    no-alloc entry point: run the dense gradient on cuda:0, then on cuda:1, in the same process."""
+    import ctypes as C
+    from erasurehead_b200.ops import _lib, grad as gops
+    L = _lib.lib()
+    outs = []
+    try:
+        for dev in ("cuda:0", "cuda:1"):
+            torch.cuda.set_device(dev)
+            g = torch.Generator(device="cpu").manual_seed(3)
+            X = (torch.randn(4096, 2048, generator=g) / 45.0).to(dev)
+            y = torch.sign(torch.randn(4096, generator=g)).to(dev)
+            beta = torch.randn(2048, generator=g).to(dev)
+            a = gops.grad_dense(X, y, beta)
+            b = torch.full((2048,), float("nan"), device=dev)
+            job = gops.make_dense_job([X], [y], beta.data_ptr(), b.data_ptr(), 2048, [1.0], 0)
+            _lib.check(L.eh_grad_dense_noalloc(C.byref(job), torch.cuda.current_stream().cuda_stream))
+            torch.cuda.synchronize()
+            assert torch.allclose(a, b, rtol=1e-5, atol=1e-5)
+            outs.append(a.cpu())
+        assert torch.allclose(outs[0], outs[1], rtol=1e-5, atol=1e-5)
+    finally:
+        torch.cuda.set_device(0)

@@ -22,13 +22,14 @@ def _job(X, y, beta, out, d, coeff=1.0, model=0):
     return grad.make_dense_job([X], [y], beta.data_ptr(), out.data_ptr(), d, [coeff], model)
 
 
-def _both(rows, d, seed, model=0, coeff=1.0):
+def _both(rows, d, seed, model=0, coeff=1.0, dtype=torch.float32):
     from erasurehead_b200.ops import _lib, grad, synth
     L = _lib.lib()
     torch.manual_seed(seed)
     ld = synth.pad_cols(d)
     X = torch.zeros(rows, ld, device="cuda")
     X[:, :d] = torch.randn(rows, d, device="cuda") / d ** 0.5
+    X = X.to(dtype)
     y = torch.where(torch.rand(rows, device="cuda") > 0.5, 1.0, -1.0)
     beta = torch.randn(d, device="cuda")
     ref = torch.empty(d, device="cuda")
@@ -53,6 +54,18 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     a, _ = _both(3000, 4096, 1)
     b, _ = _both(3000, 4096, 1)
     assert torch.equal(a, b)
+
+
+def test_noalloc_narrow_bf16_rows_take_the_tensor_core_kernel_through_the_same_array():
+    # bf16 rows with 96 <= ld <= 640 are routed to a different kernel (all-tcgen05, grad_mc_bf16.cu) that
+    # keeps its partial sums and barrier words in the same built-in array; then an fp32 call right after
+    for rows, d, seed, model in ((4096, 256, 5, 0), (2500, 640, 6, 1)):
+        got, ref = _both(rows, d, seed, model, 1.0, torch.bfloat16)
+        scale = max(1.0, ref.abs().max().item())
+        assert torch.isfinite(got).all()
+        assert (got - ref).abs().max().item() <= 2e-4 * scale
+    got, ref = _both(3000, 4096, 7)
+    assert (got - ref).abs().max().item() <= 2e-4 * max(1.0, ref.abs().max().item())
 
 
 def test_noalloc_rejects_shapes_beyond_the_builtin_scratch():
