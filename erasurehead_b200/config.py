@@ -108,6 +108,8 @@ class RunConfig:
     decoder: str = "concurrent"            # concurrent: the decoder runs on its own high-priority stream on SMs the
                                            # gradient kernels leave free (a round costs max(compute, wait));
                                            # inline: after the root's gradient kernels on one stream (compute + wait)
+    init: str = "scheme"                   # starting point: scheme (reference: randn for naive/replication/approx,
+                                           # zeros otherwise -- SURVEY Q8) | zeros | randn
     debug_poison: bool = False             # fill every message slot with NaN before a run (stale-read detector)
 
     def __post_init__(self):

@@ -125,6 +125,26 @@ class NcclBaselineEngine:
             self._round(self._cursor)
             self._cursor += 1
 
+    def run(self, rounds: int):
+        """Run ``rounds`` rounds keeping every iterate and a CUDA-event time per round (max over ranks).
+        Returns ``(betaset [R, d] float64, timeset [R] seconds)`` on the root, else ``(None, timeset)``."""
+        self.prepare()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(rounds + 1)]
+        keep = torch.zeros((rounds, self.cfg.n_cols), dtype=torch.float64, device=self.dev) if self.ctx.is_root else None
+        ev[0].record()
+        for r in range(rounds):
+            self._round(self._cursor)
+            self._cursor += 1
+            if keep is not None:
+                keep[r].copy_(self.beta)
+            ev[r + 1].record()
+        torch.cuda.synchronize()
+        ts = torch.tensor([ev[r].elapsed_time(ev[r + 1]) * 1e-3 for r in range(rounds)], dtype=torch.float64,
+                          device=self.dev)
+        if self.ctx.world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        return (keep.cpu().numpy() if keep is not None else None), ts.cpu().numpy()
+
     def step(self):
         i = self._cursor
         self.enqueue(1)

@@ -164,6 +164,10 @@ def build_scheme(cfg: RunConfig, B: Optional[np.ndarray] = None) -> SchemeSpec:
         need_count, need_groups, decode = max(1, cfg.num_collect), n_groups, DECODE_FIRST_PER_GROUP
 
     beta0 = "randn" if name in ("naive", "replication", "approx") else "zeros"   # Q8
+    if getattr(cfg, "init", "scheme") != "scheme":
+        if cfg.init not in ("zeros", "randn"):
+            raise ValueError("init must be scheme, zeros or randn")
+        beta0 = cfg.init
 
     prefix = {
         "naive": "naive_acc",
