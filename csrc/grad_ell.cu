@@ -312,6 +312,259 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Fixed-point shared-memory variant (d <= ~28K: Covertype- and KC-House-shaped data).
+//
+// fp32 atomicAdd on shared memory is not a hardware operation on sm_100 (SASS: an
+// ATOMS.CAST.SPIN compare-and-swap loop), a 32-bit integer add is (ATOMS.ADD).  So the scatter
+// accumulates every addend as a fixed-point integer split over two 32-bit words,
+//
+//     v = round(rs * 2^S),  |v| <= 2^W,      hi += v >> LB,   lo += v & (2^LB - 1)
+//
+// with S from a bound on |rs| (|coeff| * |y|max for the logistic residual, 2 |coeff| (|y|max +
+// nnz * |beta|max) for the linear one) and W / LB from the number of rows a CTA adds up so that
+// neither word can overflow (rows <= 65536: W = 30, LB = 16 -- 30 bits below the bound, finer
+// than the fp32 mantissa).  Integer adds commute exactly, so the per-CTA sums -- and after the
+// fixed-order combination of the CTAs of a message, the result -- are bitwise reproducible
+// whatever order the warps run in.  The hot loop is branch-free (padding lanes of a row go to a
+// dummy column, the bias column is an ordinary column), uses 32-bit row arithmetic only, and
+// requests the next four rows of a warp before it processes the current four.
+// No reference counterpart (scipy CSR^T matvec in float64, approximate_coding.py:194-196).
+// ---------------------------------------------------------------------------------------------
+template <bool BETA_IN_SMEM, bool WIDE>
+__global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllParams p, float* __restrict__ partials) {
+    extern __shared__ __align__(16) float ges_smem[];
+    // hi[d + 1], lo[d + 1] accumulator words (separate arrays: consecutive columns fall into consecutive banks),
+    // then [d + 1] parameters; slot d is a dummy column that absorbs the padding lanes (a row of 55 ones
+    // occupies 64 lanes) so the hot loop has no branches
+    const int dd = ((p.d + 1) + 3) & ~3;
+    int* acc_hi = reinterpret_cast<int*>(ges_smem);
+    int* acc_lo = acc_hi + dd;
+    float* bsm = ges_smem + 2 * dd;
+    __shared__ uint32_t s_code;
+    __shared__ float s_red[2][GES_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int G = gridDim.x, b = blockIdx.x;
+
+    for (int c = tid; c <= p.d; c += GES_THREADS) { acc_hi[c] = 0; acc_lo[c] = 0; }
+
+    // which batched message this CTA works for
+    int jb = 0;
+    while (jb + 1 < p.n_jobs && b >= p.job_cta0[jb + 1]) ++jb;
+    const int b0 = p.job_cta0[jb], Gj = p.job_cta0[jb + 1] - b0, bl = b - b0, seg0 = p.job_seg0[jb];
+    // 32-bit row arithmetic throughout (the host checks rows < 2^31): a 64-bit division per row costs more
+    // instructions than the rest of the row's work
+    const int rps = p.rows_per_seg;
+    const int job_rows = rps * p.job_nsegs[jb];
+    const int gwarp = bl * (GES_THREADS / 32) + warp;
+    const int nwarps = Gj * (GES_THREADS / 32);
+    constexpr int RW = 4;                      // rows per warp and step
+    const int nnz = p.nnz, dummy = p.d;
+
+    // |y|max over this CTA's rows and |coeff|max over the message's partitions (independent of the parameters)
+    float ymax = 0.f, cmax = 0.f;
+    for (int i = 0; i < p.job_nsegs[jb]; ++i) cmax = fmaxf(cmax, fabsf(p.coeff[seg0 + i]));
+    {   // lane-parallel over this warp's rows: 32 independent label loads per step
+        const int stride = nwarps * RW;
+        const int n_sets = (job_rows - gwarp * RW + stride - 1) / stride;          // <= 0 if the warp has no rows
+        for (int k = lane; k < n_sets * RW; k += 32) {
+            const int row = gwarp * RW + (k / RW) * stride + (k % RW);
+            if (row < job_rows) ymax = fmaxf(ymax, fabsf(__ldg(p.seg_y[seg0 + row / rps] + row % rps)));
+        }
+    }
+
+    if (tid == 0) {
+        uint32_t code = GE_GO;
+        if (b == 0) {
+            if (p.beta_flag) {
+                const uint64_t t0 = globaltimer();
+                while (true) {
+                    const uint32_t f = ld_acquire_sys(p.beta_flag);
+                    if (f == p.stamp) break;
+                    if (f > p.stamp) { code = GE_SKIP; break; }
+                    if (p.err && ld_acquire_sys(p.err) != 0) { code = GE_SKIP; break; }
+                    if (globaltimer() - t0 > p.timeout_ns) {
+                        if (p.err) atomicCAS(p.err, 0u, (uint32_t)(-EH_ETIMEOUT));
+                        code = GE_SKIP;
+                        break;
+                    }
+                    nanosleep(64);
+                }
+            }
+            st_release_gpu(&p.hdr->decision, (p.seq << 2) | code);
+        } else {
+            uint32_t v;
+            while (((v = ld_acquire_gpu(&p.hdr->decision)) >> 2) != p.seq) nanosleep(32);
+            code = v & 3u;
+        }
+        s_code = code;
+    }
+    __syncthreads();
+    if (s_code == GE_SKIP) return;
+
+    // parameters -> shared memory (if they fit); |beta|max is needed only for the linear residual's bound
+    float bmax = 0.f;
+    if (BETA_IN_SMEM) {
+        for (int c = tid; c < p.d; c += GES_THREADS) {
+            const float t = __ldcg(p.beta + c);
+            bsm[c] = t;
+            bmax = fmaxf(bmax, fabsf(t));
+        }
+        if (tid == 0) bsm[dummy] = 0.f;
+    } else if (p.model != EH_MODEL_LOGISTIC) {
+        for (int c = tid; c < p.d; c += GES_THREADS) bmax = fmaxf(bmax, fabsf(__ldcg(p.beta + c)));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+        bmax = fmaxf(bmax, __shfl_xor_sync(0xffffffffu, bmax, o));
+    }
+    if (lane == 0) { s_red[0][warp] = ymax; s_red[1][warp] = bmax; }
+    __syncthreads();
+    ymax = 0.f; bmax = 0.f;
+#pragma unroll
+    for (int w = 0; w < GES_THREADS / 32; ++w) { ymax = fmaxf(ymax, s_red[0][w]); bmax = fmaxf(bmax, s_red[1][w]); }
+    // bound on |rs| and the fixed-point format
+    float bound = (p.model == EH_MODEL_LOGISTIC) ? cmax * ymax : 2.0f * cmax * (ymax + (float)nnz * bmax);
+    if (!(bound > 1e-30f)) bound = 1e-30f;
+    int e2;
+    frexpf(bound, &e2);                                            // bound < 2^e2
+    const long long rows_cta = (long long)((job_rows + nwarps * RW - 1) / (nwarps * RW)) * (GES_THREADS / 32) * RW;
+    int R2 = 0;
+    while ((1ll << R2) < rows_cta) ++R2;
+    const int LB = R2 <= 16 ? 16 : 32 - R2;
+    const int W = R2 <= 16 ? 30 : 63 - 2 * R2;                     // rows * 2^LB < 2^32 and rows * 2^(W-LB) < 2^31
+    const float scale = ldexpf(1.0f, W - e2);
+    const unsigned lo_mask = (1u << LB) - 1u;
+
+    struct RowSet {
+        int c0[RW], c1[RW];
+        float yv[RW], cf[RW];
+        const int32_t* rip[RW];
+    };
+    const bool l0 = lane < nnz, l1 = lane + 32 < nnz;
+    // (sg, lr) = partition and local row of the first row of a set, advanced without divisions
+    auto load_rows = [&](int row0, int sg0, int lr0, RowSet& R) {
+#pragma unroll
+        for (int r = 0; r < RW; ++r) {
+            const bool valid = row0 + r < job_rows;
+            int sg = sg0, lr = lr0 + r;
+            while (valid && lr >= rps) { lr -= rps; ++sg; }
+            if (!valid) { sg = sg0; lr = lr0; }
+            const int32_t* ri = p.seg_idx[sg] + (size_t)lr * nnz;
+            R.rip[r] = ri;
+            R.c0[r] = (valid && l0) ? __ldg(ri + lane) : dummy;
+            R.c1[r] = (valid && l1) ? __ldg(ri + lane + 32) : dummy;
+            R.yv[r] = __ldg(p.seg_y[sg] + lr);
+            R.cf[r] = valid ? p.coeff[sg] : 0.f;
+        }
+    };
+    auto gather = [&](int c) -> float {
+        if (BETA_IN_SMEM) return bsm[c];
+        return c < dummy ? __ldcg(p.beta + c) : 0.f;
+    };
+    auto process = [&](const RowSet& R, int row0) {
+        float s[RW];
+#pragma unroll
+        for (int r = 0; r < RW; ++r) {
+            float t = gather(R.c0[r]) + gather(R.c1[r]);
+            if (WIDE) {
+                if (row0 + r < job_rows)
+                    for (int k = lane + 64; k < nnz; k += 32) t += gather(__ldg(R.rip[r] + k));
+            }
+            s[r] = t;
+        }
+        // four row sums with 6 shuffles instead of 20: the halves of the warp trade rows (0,1 <-> 2,3), then the
+        // quarters (0 <-> 1, 2 <-> 3), then three butterflies inside each group of 8 lanes; lane group g = lane / 8
+        // ends up with the margin of row g, evaluates that row's residual once, and the four fixed-point values
+        // are broadcast back
+        static_assert(RW == 4, "the row-sum exchange below is written for four rows");
+        const bool up = lane & 16, q1 = lane & 8;
+        float a0 = (up ? s[2] : s[0]) + __shfl_xor_sync(0xffffffffu, up ? s[0] : s[2], 16);
+        float a1 = (up ? s[3] : s[1]) + __shfl_xor_sync(0xffffffffu, up ? s[1] : s[3], 16);
+        float m = (q1 ? a1 : a0) + __shfl_xor_sync(0xffffffffu, q1 ? a0 : a1, 8);
+        m += __shfl_xor_sync(0xffffffffu, m, 4);
+        m += __shfl_xor_sync(0xffffffffu, m, 2);
+        m += __shfl_xor_sync(0xffffffffu, m, 1);
+        const int g = lane >> 3;
+        const float my_y = g == 0 ? R.yv[0] : g == 1 ? R.yv[1] : g == 2 ? R.yv[2] : R.yv[3];
+        const float my_cf = g == 0 ? R.cf[0] : g == 1 ? R.cf[1] : g == 2 ? R.cf[2] : R.cf[3];
+        const int my_v = __float2int_rn(my_cf * ell_residual(p.model, m, my_y) * scale);
+#pragma unroll
+        for (int r = 0; r < RW; ++r) {
+            const int v = __shfl_sync(0xffffffffu, my_v, 8 * r);
+            const int vh = v >> LB;
+            const int vl = (int)((unsigned)v & lo_mask);
+            atomicAdd(acc_hi + R.c0[r], vh); atomicAdd(acc_lo + R.c0[r], vl);
+            atomicAdd(acc_hi + R.c1[r], vh); atomicAdd(acc_lo + R.c1[r], vl);
+            if (WIDE) {
+                if (row0 + r < job_rows)
+                    for (int k = lane + 64; k < nnz; k += 32) {
+                        const int c = __ldg(R.rip[r] + k);
+                        atomicAdd(acc_hi + c, vh); atomicAdd(acc_lo + c, vl);
+                    }
+            }
+        }
+    };
+    RowSet A, B;
+    const int step = nwarps * RW;
+    int row0 = gwarp * RW;
+    int sg_n = seg0 + row0 / rps, lr_n = row0 % rps;             // position of the set being loaded next
+    auto advance = [&]() {
+        lr_n += step;
+        while (lr_n >= rps) { lr_n -= rps; ++sg_n; }
+    };
+    if (row0 < job_rows) {
+        load_rows(row0, sg_n, lr_n, A);
+        advance();
+        while (true) {                                           // two sets ping-pong: no register copies
+            if (row0 + step < job_rows) { load_rows(row0 + step, sg_n, lr_n, B); advance(); }
+            process(A, row0);
+            row0 += step;
+            if (row0 >= job_rows) break;
+            if (row0 + step < job_rows) { load_rows(row0 + step, sg_n, lr_n, A); advance(); }
+            process(B, row0);
+            row0 += step;
+            if (row0 >= job_rows) break;
+        }
+    }
+    __syncthreads();
+    float* mine = partials + (size_t)b * p.d;
+    const double inv = (double)ldexpf(1.0f, e2 - W);
+    const double hi_w = (double)(1u << LB);
+    for (int c = tid; c < p.d; c += GES_THREADS) {
+        __stcg(mine + c, (float)(((double)acc_hi[c] * hi_w + (double)(unsigned)acc_lo[c]) * inv));
+    }
+
+    uint32_t gen = 0;
+    grid_barrier(&p.hdr->barrier, gen);
+
+    // ordered reduction per message: CTA bl of the message owns a contiguous column range
+    const int chunk = (p.d + Gj - 1) / Gj;
+    const int c0 = bl * chunk, c1 = min(p.d, c0 + chunk);
+    float* out = p.job_out[jb];
+    for (int c = c0 + tid; c < c1; c += GES_THREADS) {
+        float t = 0.f;
+        for (int g = b0; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
+        out[c] = t;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence_system();
+        const uint32_t old = atom_add_acq_rel_gpu(&p.hdr->done, 1u);
+        if (old == (uint32_t)G - 1) {
+            p.hdr->barrier = 0;
+            p.hdr->done = 0;
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_arrival_time(p.job_flag[j]);
+            __threadfence_system();
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);       // ordered by the fence above
+        }
+    }
+}
+
 constexpr size_t GES_SMEM_LIMIT = 224 * 1024;
 
 }  // namespace eh
@@ -336,6 +589,7 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
     const eh_grad_ell_job* j = &jobs[0];
     EH_REQUIRE(j->d_beta, "grad_ell: null pointer");
     EH_REQUIRE(j->rows_per_seg > 0 && j->d > 0 && j->nnz > 0, "grad_ell: empty problem");
+    EH_REQUIRE((long long)j->rows_per_seg * GE_MAX_SEGS < (1ll << 31), "grad_ell: more than 2^31 rows in one launch");
     EH_REQUIRE(scratch_bytes >= eh_grad_ell_scratch_bytes(j->d), "grad_ell: scratch too small");
     const DevInfo& di = dev_info();
     const size_t acc_bytes = (size_t)((j->d + 3) & ~3) * sizeof(float);
@@ -379,9 +633,12 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
     p.rows_per_seg = j->rows_per_seg; p.n_segs = j->n_segs;
     p.model = j->model; p.bias_col = j->bias_col; p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
+    // fixed-point variant (native integer shared-memory atomics) when two words per column fit
+    const size_t fx_col_bytes = (size_t)(((j->d + 1) + 3) & ~3) * sizeof(float);      // one word per column incl. the dummy
+    const bool fx_variant = smem_variant && 2 * fx_col_bytes <= GES_SMEM_LIMIT && getenv("EH_ELL_FLOAT_ATOMICS") == nullptr;
     if (smem_variant) {
-        const bool both = 2 * acc_bytes <= GES_SMEM_LIMIT;
-        const size_t smem = both ? 2 * acc_bytes : acc_bytes;
+        const bool both = fx_variant ? 3 * fx_col_bytes <= GES_SMEM_LIMIT : 2 * acc_bytes <= GES_SMEM_LIMIT;
+        const size_t smem = fx_variant ? (both ? 3 : 2) * fx_col_bytes : (both ? 2 * acc_bytes : acc_bytes);
         // CTAs per message in proportion to its rows (32 rows of work per warp at least), every message >= 1
         const long long total_rows = (long long)j->rows_per_seg * nseg;
         long long grid = worker_sms();
@@ -399,9 +656,18 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
         float* partials = p.gacc;
         EH_REQUIRE(scratch_bytes >= sizeof(EllScratchHdr) + (size_t)grid * j->d * sizeof(float),
                    "grad_ell: scratch too small for the shared-memory variant");
-        const void* kern = both ? (const void*)grad_ell_smem_kernel<true> : (const void*)grad_ell_smem_kernel<false>;
-        if (both) { EH_SET_MAX_SMEM((grad_ell_smem_kernel<true>), (int)GES_SMEM_LIMIT); }
-        else { EH_SET_MAX_SMEM((grad_ell_smem_kernel<false>), (int)GES_SMEM_LIMIT); }
+        const void* kern;
+        if (fx_variant) {
+            const bool wide = j->nnz > 64;
+            if (both && !wide) { kern = (const void*)grad_ell_fx_kernel<true, false>; EH_SET_MAX_SMEM((grad_ell_fx_kernel<true, false>), (int)GES_SMEM_LIMIT); }
+            else if (both) { kern = (const void*)grad_ell_fx_kernel<true, true>; EH_SET_MAX_SMEM((grad_ell_fx_kernel<true, true>), (int)GES_SMEM_LIMIT); }
+            else if (!wide) { kern = (const void*)grad_ell_fx_kernel<false, false>; EH_SET_MAX_SMEM((grad_ell_fx_kernel<false, false>), (int)GES_SMEM_LIMIT); }
+            else { kern = (const void*)grad_ell_fx_kernel<false, true>; EH_SET_MAX_SMEM((grad_ell_fx_kernel<false, true>), (int)GES_SMEM_LIMIT); }
+        } else {
+            kern = both ? (const void*)grad_ell_smem_kernel<true> : (const void*)grad_ell_smem_kernel<false>;
+            if (both) { EH_SET_MAX_SMEM((grad_ell_smem_kernel<true>), (int)GES_SMEM_LIMIT); }
+            else { EH_SET_MAX_SMEM((grad_ell_smem_kernel<false>), (int)GES_SMEM_LIMIT); }
+        }
         void* args[] = {(void*)&p, (void*)&partials};
         return launch_grid_sync(kern, dim3((unsigned)grid), dim3(GES_THREADS), args, smem, (cudaStream_t)stream);
     }

@@ -69,6 +69,32 @@ def test_grad_ell_matches_reference(model):
     assert (g.double() - want).abs().max().item() <= 5e-4 * max(1.0, want.abs().max().item())
 
 
+@pytest.mark.parametrize("model", [0, 1])
+def test_grad_ell_fixed_point_scatter_is_exactly_reproducible(model):
+    """Covertype-sized feature space: the shared-memory scatter adds fixed-point integers (native
+    ATOMS.ADD), so two runs agree bit for bit whatever order the warps ran in, and the result is at
+    least as close to float64 as an fp32 accumulation (large and small encode weights together)."""
+    from erasurehead_b200.data import generate_onehot
+    from erasurehead_b200.ops import grad
+    d, nnz = 15509, 55
+    ds = generate_onehot(3 * 9000, d, nnz, 3, seed=4, task="linear" if model else "logistic")
+    idxs = [torch.from_numpy(ds.ell(p)).to(DEV) for p in range(3)]
+    ys = [torch.tensor(ds.labels(p), dtype=torch.float32, device=DEV) for p in range(3)]
+    beta = torch.randn(d, device=DEV) * 0.2
+    cf = [1.0, -37.5, 0.003]
+    g1 = grad.grad_ell(idxs, ys, beta, coeff=cf, model=model, bias_col=d - 1)
+    g2 = grad.grad_ell(idxs, ys, beta, coeff=cf, model=model, bias_col=d - 1)
+    assert torch.equal(g1, g2)
+    Xs = [torch.sparse_csr_tensor(torch.arange(0, i.numel() + 1, nnz, device=DEV), i.reshape(-1).long(),
+                                  torch.ones(i.numel(), dtype=torch.float64, device=DEV), size=(i.shape[0], d)) for i in idxs]
+    want = torch.zeros(d, dtype=torch.float64, device=DEV)
+    for X, y, c in zip(Xs, ys, cf):
+        pm = torch.mv(X, beta.double())
+        r = -y.double() / (torch.exp(pm * y.double()) + 1) if model == 0 else -2 * (y.double() - pm)
+        want += c * torch.mv(X.t().to_sparse_csr(), r)
+    assert (g1.double() - want).abs().max().item() <= 2e-5 * max(1.0, want.abs().max().item())
+
+
 @pytest.mark.parametrize("d", [5000, 70000])
 def test_grad_ell_multi_batches_messages_in_one_launch(d):
     """Several one-hot messages (different partition counts / coefficients) in one launch; d = 70000 does
