@@ -20,7 +20,7 @@ N_COLS=${N_COLS:-27654}
 # | 1 0 0 cyclic MDS | 1 0 2 ignore stragglers | 1 P 0 partial coded | 1 P 1 partial replication
 MODE=${MODE:-"1 0 3"}
 read IS_CODED PARTS CODED_VER <<< "$MODE"
-HOSTFILE=${HOSTFILE:-}            # optional: one host per line -> multi-node via tools/cluster.py
+HOSTFILE=${HOSTFILE:-}            # optional: one host per line -> one independent single-node job per host (tools/cluster.py torchrun)
 EXTRA="$@"
 
 cd "$(dirname "$0")/.."

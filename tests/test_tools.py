@@ -48,3 +48,68 @@ def test_command_map_covers_the_reference(monkeypatch, tmp_path):
     monkeypatch.chdir(tmp_path)
     cluster.main(["clean_launch_and_run", "--count", "2", "--", "main.py", "9"])
     assert calls == ["cmd_shutdown", "cmd_launch", "wait", "cmd_get_hosts", "cmd_bootstrap", "cmd_install", "cmd_torchrun"]
+
+
+class _FakeEc2:
+    """Records the boto3 calls of the launch path; spot requests become active on the second poll."""
+
+    def __init__(self):
+        self.calls, self.polls = [], 0
+
+    def request_spot_instances(self, **kw):
+        self.calls.append(("request_spot_instances", kw))
+        return {"SpotInstanceRequests": [{"SpotInstanceRequestId": f"sir-{i}"} for i in range(kw["InstanceCount"])]}
+
+    def describe_spot_instance_requests(self, **kw):
+        self.polls += 1
+        ids = kw.get("SpotInstanceRequestIds") or ["sir-0"]
+        done = self.polls >= 2
+        return {"SpotInstanceRequests": [
+            {"SpotInstanceRequestId": i, "State": "active" if done else "open", "InstanceId": "i-" + i[4:] if done else None,
+             "Status": {"Code": "fulfilled" if done else "pending-evaluation", "Message": ""},
+             "LaunchSpecification": {"KeyName": "k"}} for i in ids]}
+
+    def create_tags(self, **kw):
+        self.calls.append(("create_tags", kw))
+
+    def run_instances(self, **kw):
+        self.calls.append(("run_instances", kw))
+        return {"Instances": [{"InstanceId": "i-x"}]}
+
+    def cancel_spot_instance_requests(self, **kw):
+        self.calls.append(("cancel_spot_instance_requests", kw))
+
+
+def test_spot_launch_requests_waits_and_tags(monkeypatch):
+    """The reference's default launch method (pytorch_ec2.py:29,39,176-205): request_spot_instances with the
+    price as a string, poll until fulfilled, then tag; `ondemand` goes through run_instances."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import time
+    import cluster
+    fake = _FakeEc2()
+    monkeypatch.setattr(cluster, "_ec2", lambda: fake)
+    monkeypatch.setattr(time, "sleep", lambda s: None)
+    monkeypatch.setitem(cluster.cfg, "key_name", "k")
+    cluster.main(["launch", "--count", "3", "--method", "spot", "--spot-price", "12.5"])
+    name, kw = fake.calls[0]
+    assert name == "request_spot_instances" and kw["InstanceCount"] == 3 and kw["SpotPrice"] == "12.5"
+    assert kw["LaunchSpecification"]["InstanceType"] == cluster.cfg["instance_type"]
+    assert fake.polls == 2
+    assert fake.calls[1][0] == "create_tags" and fake.calls[1][1]["Resources"] == ["i-0", "i-1", "i-2"]
+    fake.calls.clear()
+    cluster.main(["launch", "--count", "2", "--method", "ondemand"])
+    assert fake.calls[0][0] == "run_instances" and fake.calls[0][1]["MinCount"] == 2
+    fake.calls.clear()
+    assert cluster.cancel_spot_requests(fake) == ["sir-0"]
+
+
+def test_torchrun_starts_one_single_node_job_per_host():
+    """All ranks of a process group must share a node (parallel/workspace.py refuses anything else), so the
+    multi-host launcher starts independent single-node jobs; {node} expands per host."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    c0 = cluster.torchrun_command(0, 2, "/repo", 8, 29500, ["main.py", "9", "--seed={node}", "--output-dir=out{node}of{nodes}"])
+    c1 = cluster.torchrun_command(1, 2, "/repo", 8, 29500, ["main.py", "9", "--seed={node}"])
+    for c in (c0, c1):
+        assert "--nnodes=1 " in c and "--master-addr 127.0.0.1" in c and "--node-rank" not in c
+    assert "--seed=0" in c0 and "--output-dir=out0of2" in c0 and "--seed=1" in c1 and "run_node1.log" in c1

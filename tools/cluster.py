@@ -4,7 +4,12 @@
 Sub-commands mirror the reference's command map (pytorch_ec2.py:938-951) where they still make
 sense for GPU nodes:
 
-  launch / shutdown / list_running_instances   EC2 instances through boto3 (only if boto3 is installed)
+  launch [--method spot|ondemand] / shutdown / list_running_instances
+                                               EC2 instances through boto3 (only if boto3 is installed).  Spot
+                                               (the reference's default, pytorch_ec2.py:29,39,176-205): one request of
+                                               `--count` instances at `--spot-price`, wait until every request is
+                                               fulfilled, tag the instances; shutdown also cancels open spot requests
+                                               (terminate_all_requests, :129-154)
   get_hosts                                    write ``hosts``, ``hosts_alias``, ``hosts_address`` (:656-708)
   run_command  <hostfile> -- <cmd>             run a shell command on every host (paramiko SSH fan-out, :259-299)
   list_idle_instances <hostfile>               hosts with no GPU compute process (:304-336)
@@ -19,7 +24,10 @@ sense for GPU nodes:
                                                shutdown, launch, wait until every instance is up and reachable,
                                                get_hosts, bootstrap, install, torchrun (pytorch_ec2.py:938 map entry)
   torchrun --hostfile F --gpus-per-node G -- main.py <13 positionals>
-                                               multi-node launch: one ``torch.distributed.run`` per host
+                                               one INDEPENDENT single-node ``torch.distributed.run`` job per host (the
+                                               NVLink peer-memory transport lives inside one node,
+                                               parallel/workspace.py); ``{node}`` / ``{nodes}`` in the arguments expand
+                                               to the host's index / the host count (seeds, output directories)
 
 Unlike the reference, processes are never killed by pattern (``pkill python``): the launcher
 records the PID it started on every host under ``~/.erasurehead_b200/pids`` and only those are
@@ -49,6 +57,9 @@ cfg = Cfg({
     "name": "erasurehead", "region": "us-west-2", "availability_zone": "us-west-2b",
     "instance_type": "p6-b200.48xlarge", "image_id": "", "key_name": "", "ssh_username": "ubuntu",
     "n_workers": 1, "nfs_mount_point": "/shared", "repo_dir": "%(nfs_mount_point)s/%(name)s",
+    "method": "ondemand",          # "spot" is the reference's default (pytorch_ec2.py:29); GPU capacity is usually reserved
+    "spot_price": "",              # max price per instance-hour as a string (pytorch_ec2.py:39); "" = on-demand price cap
+    "security_groups": ["default"],
 })
 
 
@@ -92,14 +103,73 @@ def _ec2():
     return boto3.client("ec2", region_name=cfg["region"])
 
 
+def launch_spec(count: int) -> dict:
+    """Arguments shared by both launch methods (the reference's `launch_specs`, pytorch_ec2.py:184-188)."""
+    return {"ImageId": cfg["image_id"], "InstanceType": cfg["instance_type"], "KeyName": cfg["key_name"],
+            "Placement": {"AvailabilityZone": cfg["availability_zone"]}, "SecurityGroups": list(cfg["security_groups"])}
+
+
+def spot_request_args(count: int, price: str) -> dict:
+    args = {"InstanceCount": count, "Type": "one-time", "LaunchSpecification": launch_spec(count)}
+    if price:
+        args["SpotPrice"] = str(price)
+    return args
+
+
+def wait_spot_fulfilled(ec2, request_ids, timeout_s: int = 1800, poll_s: int = 10, sleep=None):
+    """Poll the spot requests until every one is `active` (fulfilled); print state - status lines like the
+    reference's wait_until_instance_request_status_fulfilled (pytorch_ec2.py:232-256).  A request that
+    ends `closed` / `cancelled` / `failed` aborts.  Returns the instance ids."""
+    import time
+    sleep = sleep or time.sleep
+    t0 = time.time()
+    while True:
+        r = ec2.describe_spot_instance_requests(SpotInstanceRequestIds=list(request_ids))
+        reqs = r["SpotInstanceRequests"]
+        for q in reqs:
+            st = q.get("Status", {})
+            print(f"{q['SpotInstanceRequestId']} {q['State']} - {st.get('Code', '')}: {st.get('Message', '')}")
+        bad = [q for q in reqs if q["State"] in ("closed", "cancelled", "failed")]
+        if bad:
+            sys.exit(f"spot request {bad[0]['SpotInstanceRequestId']} ended {bad[0]['State']}: "
+                     f"{bad[0].get('Status', {}).get('Message', '')}")
+        if reqs and all(q["State"] == "active" and q.get("InstanceId") for q in reqs):
+            return [q["InstanceId"] for q in reqs]
+        if time.time() - t0 > timeout_s:
+            sys.exit(f"spot requests not fulfilled within {timeout_s} s")
+        sleep(poll_s)
+
+
+def cancel_spot_requests(ec2):
+    """Cancel this cluster's open/active spot requests (terminate_all_requests, pytorch_ec2.py:129-154);
+    requests are recognised by the launch specification's key name, as in the reference."""
+    r = ec2.describe_spot_instance_requests(Filters=[{"Name": "state", "Values": ["open", "active"]}])
+    ids = [q["SpotInstanceRequestId"] for q in r["SpotInstanceRequests"]
+           if q.get("LaunchSpecification", {}).get("KeyName") == cfg["key_name"]]
+    if ids:
+        ec2.cancel_spot_instance_requests(SpotInstanceRequestIds=ids)
+    print("cancelled spot requests", ids)
+    return ids
+
+
 def cmd_launch(a):
     ec2 = _ec2()
-    r = ec2.run_instances(ImageId=cfg["image_id"], InstanceType=cfg["instance_type"], KeyName=cfg["key_name"],
-                          MinCount=a.count, MaxCount=a.count,
-                          Placement={"AvailabilityZone": cfg["availability_zone"]},
-                          TagSpecifications=[{"ResourceType": "instance",
-                                              "Tags": [{"Key": "Name", "Value": cfg["name"]}]}])
-    print("launched", [i["InstanceId"] for i in r["Instances"]])
+    method = getattr(a, "method", None) or cfg["method"]
+    tags = [{"Key": "Name", "Value": cfg["name"]}]
+    if method == "spot":
+        price = getattr(a, "spot_price", None) or cfg["spot_price"]
+        r = ec2.request_spot_instances(**spot_request_args(a.count, price))
+        req_ids = [q["SpotInstanceRequestId"] for q in r["SpotInstanceRequests"]]
+        print("spot requests", req_ids)
+        ids = wait_spot_fulfilled(ec2, req_ids)
+        ec2.create_tags(Resources=ids, Tags=tags)        # spot launch specifications cannot carry instance tags
+        print("launched (spot)", ids)
+    elif method in ("ondemand", "reserved"):
+        r = ec2.run_instances(MinCount=a.count, MaxCount=a.count,
+                              TagSpecifications=[{"ResourceType": "instance", "Tags": tags}], **launch_spec(a.count))
+        print("launched", [i["InstanceId"] for i in r["Instances"]])
+    else:
+        sys.exit(f"unknown launch method {method!r} (spot | ondemand)")
 
 
 def wait_until_running(count: int, timeout_s: int = 900, poll_s: int = 10):
@@ -132,6 +202,7 @@ def _instances(states=("running",)):
 
 
 def cmd_shutdown(a):
+    cancel_spot_requests(_ec2())
     ids = [i["InstanceId"] for i in _instances(("running", "pending"))]
     if ids:
         _ec2().terminate_instances(InstanceIds=ids)
@@ -220,25 +291,28 @@ def cmd_clean_launch_and_run(a):
     cmd_torchrun(a)
 
 
+def torchrun_command(host_index: int, n_hosts: int, repo: str, gpus_per_node: int, port: int, rest: List[str]) -> str:
+    """Shell command for ONE host: an independent single-node job (all ranks of a process group must share
+    a node, parallel/workspace.py).  `{node}` and `{nodes}` in the arguments become the host's index and the
+    host count, so that hosts can run different seeds / configurations / output directories."""
+    args = " ".join(shlex.quote(x.replace("{node}", str(host_index)).replace("{nodes}", str(n_hosts))) for x in rest)
+    return (f"mkdir -p {PID_DIR} && cd {repo} && setsid python -m torch.distributed.run --nnodes=1 "
+            f"--nproc-per-node={gpus_per_node} --master-addr 127.0.0.1 --master-port {port} {args} "
+            f"> run_node{host_index}.log 2>&1 & echo $! > {PID_DIR}/run.pid; wait; tail -5 run_node{host_index}.log")
+
+
 def cmd_torchrun(a):
     hosts = read_hosts(a.hostfile)
-    master = hosts[0]
     repo = a.repo or os.getcwd()
-    args = " ".join(shlex.quote(x) for x in a.rest)
-
-    def command(h):
-        rank = hosts.index(h)
-        return (f"mkdir -p {PID_DIR} && cd {repo} && setsid python -m torch.distributed.run --nnodes={len(hosts)} "
-                f"--node-rank={rank} --nproc-per-node={a.gpus_per_node} --master-addr {master} "
-                f"--master-port {a.port} {args} > run_node{rank}.log 2>&1 & echo $! > {PID_DIR}/run.pid; wait; "
-                f"tail -5 run_node{rank}.log")
-    fan_out(hosts, command)
+    fan_out(hosts, lambda h: torchrun_command(hosts.index(h), len(hosts), repo, a.gpus_per_node, a.port, a.rest))
 
 
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     sub = ap.add_subparsers(dest="cmd", required=True)
-    p = sub.add_parser("launch"); p.add_argument("--count", type=int, default=cfg["n_workers"]); p.set_defaults(fn=cmd_launch)
+    p = sub.add_parser("launch"); p.add_argument("--count", type=int, default=cfg["n_workers"])
+    p.add_argument("--method", choices=["spot", "ondemand", "reserved"]); p.add_argument("--spot-price")
+    p.set_defaults(fn=cmd_launch)
     sub.add_parser("shutdown").set_defaults(fn=cmd_shutdown)
     sub.add_parser("list_running_instances").set_defaults(fn=cmd_list_running)
     p = sub.add_parser("get_hosts"); p.add_argument("--hostfile"); p.set_defaults(fn=cmd_get_hosts)
@@ -252,6 +326,7 @@ def main(argv=None):
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
     p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_torchrun)
     p = sub.add_parser("clean_launch_and_run"); p.add_argument("--count", type=int, default=cfg["n_workers"])
+    p.add_argument("--method", choices=["spot", "ondemand", "reserved"]); p.add_argument("--spot-price")
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
     p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_clean_launch_and_run)
     a = ap.parse_args(argv)
