@@ -36,13 +36,15 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
         // <= 32 partitions), and so are one-hot messages; multi-column messages get their own kernels
         eh_grad_job batch[8];
         eh_grad_ell_job ebatch[8];
-        int nb = 0, nb_segs = 0, ne = 0, ne_segs = 0;
+        int nb = 0, nb_segs = 0, ne = 0, ne_segs = 0, e_classes = 0;     // e_classes > 0: the one-hot batch is multi-column
         auto flush = [&]() -> int {
             int rc = EH_OK;
             if (nb > 0) rc = eh_grad_dense_multi(batch, nb, plan->d_scratch, plan->scratch_bytes, stream);
             nb = 0; nb_segs = 0;
-            if (rc == EH_OK && ne > 0) rc = eh_grad_ell_multi(ebatch, ne, plan->d_scratch, plan->scratch_bytes, stream);
-            ne = 0; ne_segs = 0;
+            if (rc == EH_OK && ne > 0)
+                rc = e_classes > 0 ? eh_grad_ell_mc_multi(ebatch, ne, e_classes, plan->d_scratch, plan->scratch_bytes, stream)
+                                   : eh_grad_ell_multi(ebatch, ne, plan->d_scratch, plan->scratch_bytes, stream);
+            ne = 0; ne_segs = 0; e_classes = 0;
             return rc;
         };
         for (int q = 0; q < plan->n_jobs; ++q) {
@@ -108,7 +110,8 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.d_beta = beta; j.d_out = out; j.d_flag = flag; j.d_beta_flag = beta_flag; j.d_err = err;
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.nnz = wj.ld_or_nnz;
                 j.model = wj.model; j.bias_col = wj.bias_col; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
-                const bool fits = nb == 0 && ne < 8 && ne_segs + j.n_segs <= 32 &&
+                const int cls = (wj.sparse == 5) ? wj.classes : 0;
+                const bool fits = nb == 0 && ne < 8 && ne_segs + j.n_segs <= 32 && (ne == 0 || cls == e_classes) &&
                                   (ne == 0 || (ebatch[0].d == j.d && ebatch[0].nnz == j.nnz &&
                                                ebatch[0].rows_per_seg == j.rows_per_seg && ebatch[0].model == j.model &&
                                                ebatch[0].bias_col == j.bias_col));
@@ -118,6 +121,7 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 }
                 ebatch[ne++] = j;
                 ne_segs += j.n_segs;
+                e_classes = cls;
             }
             if (rc) return rc;
         }

@@ -91,6 +91,7 @@ class RunConfig:
     delay_fixed: float = 0.5               # sleep for the fixed-straggler-set variant (naive.py:143-145)
     gpus: int = 0                          # 0 = all visible
     synthetic: bool = False                # generate data on the GPU instead of reading input_dir
+    synthetic_nnz: int = 0                 # --synthetic with is_real=1: ones per row (0 = the named dataset's, data/shapes.py)
     model: Optional[str] = None            # None = reference rule (kc_house_data -> linear)
     classes: int = 1
     compat: bool = False                   # reproduce reference quirks Q1-Q3, Q9

@@ -32,11 +32,15 @@ def _column_blocks(n_cols: int, nnz: int, rng) -> np.ndarray:
 
 
 def generate_onehot(n_rows: int, n_cols: int, nnz: int, n_partitions: int, seed: int = 0,
-                    task: str = "logistic", test_frac: float = 0.25, name: str = "onehot") -> Dataset:
+                    task: str = "logistic", test_frac: float = 0.25, name: str = "onehot",
+                    classes: int = 1) -> Dataset:
+    """``task``: logistic (labels +-1), linear (real targets) or softmax (class ids ``0..classes-1`` drawn as
+    ``argmax(logits + Gumbel)`` from a hidden ``n_cols x classes`` parameter matrix)."""
     rng = np.random.RandomState(seed)
     rpp = n_rows // n_partitions                      # remainder dropped (arrange_real_data.py:79,85)
     edges = _column_blocks(n_cols, nnz, rng)
     beta_star = rng.standard_normal(n_cols) * 0.5
+    W_star = rng.standard_normal((n_cols, classes)) * 0.5 if task == "softmax" else None
 
     def draw(rows):
         idx = np.empty((rows, nnz), dtype=np.int32)
@@ -46,6 +50,9 @@ def generate_onehot(n_rows: int, n_cols: int, nnz: int, n_partitions: int, seed:
             perm_off = (z * 2654435761 + c * 97) % size      # spread the head over the block
             idx[:, c] = edges[c] + perm_off
         idx[:, nnz - 1] = n_cols - 1                  # bias column (arrange_real_data.py:55)
+        if task == "softmax":
+            logits = W_star[idx].sum(axis=1)
+            return idx, np.argmax(logits + rng.gumbel(size=logits.shape), axis=1).astype(np.float64)
         m = beta_star[idx].sum(axis=1)
         if task == "linear":
             y = m / np.sqrt(nnz) + 0.05 * rng.standard_normal(rows)

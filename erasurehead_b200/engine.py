@@ -78,6 +78,23 @@ def unpack_mc(flat: np.ndarray, d: int, C_: int) -> np.ndarray:
     return np.ascontiguousarray(np.swapaxes(W, -1, -2))
 
 
+ELL_MC_CP = 8      # padded classes per feature of the one-hot multi-column kernel (csrc/grad_ell_mc.cu)
+
+
+def pack_mc_ell(W: np.ndarray) -> np.ndarray:
+    """``[..., d, C]`` -> flat column-major ``[..., d * 8]`` (layout of csrc/grad_ell_mc.cu)."""
+    d, C_ = W.shape[-2:]
+    if C_ > ELL_MC_CP:
+        raise ValueError(f"multi-column models on one-hot features support up to {ELL_MC_CP} columns")
+    out = np.zeros(W.shape[:-2] + (d, ELL_MC_CP), dtype=W.dtype)
+    out[..., :C_] = W
+    return out.reshape(W.shape[:-2] + (-1,))
+
+
+def unpack_mc_ell(flat: np.ndarray, d: int, C_: int) -> np.ndarray:
+    return np.ascontiguousarray(flat.reshape(flat.shape[:-1] + (d, ELL_MC_CP))[..., :C_])
+
+
 class Engine:
     """Owns the device state of one run on one rank."""
 
@@ -95,12 +112,19 @@ class Engine:
         self.data = data
         self.first_round = 0
         self.on_gpu = self.ctx.device.type == "cuda"
+        self.synth_shape = self._synthetic_onehot_shape() if self.data is None else None
         if data is None and cfg.synthetic and not self.on_gpu:
-            # no GPU: --synthetic falls back to the host generator (generate_data.py distribution)
-            from .data import generate_gmm
+            # no GPU: --synthetic falls back to the host generators (generate_data.py distribution / data/shapes.py)
             task = {"linear": "linear", "softmax": "softmax"}.get(self.model.name, "logistic")
             kw = dict(classes=self.model.n_out) if task == "softmax" else {}
-            self.data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=cfg.seed or 0, task=task, **kw)
+            if self.synth_shape is not None:
+                from .data import generate_onehot
+                self.data = generate_onehot(cfg.n_rows, cfg.n_cols, self.synth_shape["nnz"], cfg.n_partitions,
+                                            seed=cfg.seed or 0, task=task, name=cfg.dataset, **kw)
+                self.synth_shape = None
+            else:
+                from .data import generate_gmm
+                self.data = generate_gmm(cfg.n_rows, cfg.n_cols, cfg.n_partitions, seed=cfg.seed or 0, task=task, **kw)
         beta0 = oracle.initial_beta(self.spec, cfg.n_cols, cfg.seed, self.model.n_out)
         self.beta0 = self.ctx.broadcast_object(beta0 if self.ctx.is_root else None)
         self.u0 = np.zeros_like(self.beta0)
@@ -115,9 +139,36 @@ class Engine:
         self.launches = 0
         # multi-column models (softmax): parameters travel as one flat class-major vector
         self.mc = self.model.n_out > 1
-        self.d_eff = _mc_flat(cfg.n_cols, self.model.n_out) if self.mc else cfg.n_cols
+        self.sparse = bool(self.data.is_sparse) if self.data is not None else self.synth_shape is not None
+        if self.mc and self.sparse:
+            if self.model.n_out > ELL_MC_CP:
+                raise ValueError(f"multi-column models on one-hot features support up to {ELL_MC_CP} columns")
+            self.d_eff = cfg.n_cols * ELL_MC_CP
+        else:
+            self.d_eff = _mc_flat(cfg.n_cols, self.model.n_out) if self.mc else cfg.n_cols
         if self.on_gpu:
             self._setup_gpu()
+
+    def _synthetic_onehot_shape(self):
+        """``--synthetic`` with ``is_real=1``: one-hot data of the named dataset's shape, generated on the
+        device (ones per row from data/shapes.py; any other dataset name needs ``--synthetic-nnz``)."""
+        cfg = self.cfg
+        if not (cfg.synthetic and cfg.is_real):
+            return None
+        from .data.shapes import DATASET_SHAPES
+        nnz = cfg.synthetic_nnz or DATASET_SHAPES.get(cfg.dataset, {}).get("nnz", 0)
+        if not nnz:
+            raise ValueError(f"--synthetic with is_real=1 needs a known dataset shape {sorted(DATASET_SHAPES)} "
+                             "or --synthetic-nnz=K (ones per row)")
+        return {"nnz": int(nnz)}
+
+    def _pack(self, W: np.ndarray) -> np.ndarray:
+        """Host ``[..., d, C]`` parameters -> the flat device layout of this run's multi-column kernel."""
+        return pack_mc_ell(W) if self.sparse else pack_mc(W)
+
+    def _unpack(self, flat: np.ndarray) -> np.ndarray:
+        f = unpack_mc_ell if self.sparse else unpack_mc
+        return f(flat, self.cfg.n_cols, self.model.n_out)
 
     # ------------------------------------------------------------------ device set-up
     def _setup_gpu(self) -> None:
@@ -143,7 +194,6 @@ class Engine:
         self.parts: Dict[int, tuple] = {}
         mine = ctx.local_workers(spec.n)
         needed = sorted({sg.partition for w in mine for sg in spec.segments[w]})
-        self.sparse = bool(self.data.is_sparse) if self.data is not None else False
         self.bf16 = cfg.dtype == "bf16" and not self.sparse
         if self.bf16 and self.mc and _pad32(cfg.n_cols) > 640:
             raise ValueError("--dtype=bf16 with a multi-column model needs n_cols <= 640 "
@@ -164,7 +214,10 @@ class Engine:
                         f"more than {_lib.EH_MAX_SEGS} partitions per message (worker {w}); "
                         "use fewer partitions per worker")
                 j = _lib.WorkerJob()
-                jkind = (4 if self.bf16 else 2) if self.mc else (1 if self.sparse else (3 if self.bf16 else 0))
+                if self.mc:
+                    jkind = 5 if self.sparse else (4 if self.bf16 else 2)
+                else:
+                    jkind = 1 if self.sparse else (3 if self.bf16 else 0)
                 j.worker, j.msg, j.sparse, j.model = w, kind, jkind, self.model.device_id
                 j.classes = self.model.n_out
                 j.n_segs, j.rows_per_seg, j.d = len(segs), spec.rows_per_part, d
@@ -179,9 +232,9 @@ class Engine:
         self.n_jobs = len(jobs)
         ld_max = max([_pad32(d)] + [self.parts[p][0].stride(0) for p in needed if not self.sparse])
         sb = max(L.eh_grad_dense_scratch_bytes(int(ld_max)), L.eh_grad_ell_scratch_bytes(int(d)))
-        if self.mc:
-            if self.sparse:
-                raise NotImplementedError("multi-column models need dense features")
+        if self.mc and self.sparse:
+            sb = max(sb, L.eh_grad_ell_mc_scratch_bytes(int(d)))
+        elif self.mc:
             sb = max(sb, L.eh_grad_mc_scratch_bytes(int(spec.rows_per_part), int(d), int(self.model.n_out)))
         self.scratch = gops.Scratch(sb, dev)
         self.timeout_ns = int(120e9)
@@ -233,6 +286,26 @@ class Engine:
             X = X.to(self.torch.bfloat16)
         return X, y
 
+    def _synth_partition(self, rows: int, p: int):
+        """Partition ``p`` (or the test set) generated on this GPU: counter-based, so a partition replicated on
+        several GPUs is bit-identical everywhere.  Dense GMM (generate_data.py distribution) or one-hot ELL of the
+        named dataset's shape; labels +-1, real targets, or class ids for a multi-column model."""
+        from .ops import synth
+        cfg, dev = self.cfg, self.ctx.device
+        if self.mc and self.model.name != "softmax":
+            raise ValueError("on-device synthetic labels exist for logistic, linear and softmax models")
+        if self.mc and self.model.n_out > 8:
+            raise ValueError("on-device synthetic multi-class labels support up to 8 classes; pass a dataset")
+        task = 2 if self.mc else (1 if self.model.name == "linear" else 0)
+        classes = self.model.n_out if self.mc else 0
+        if self.synth_shape is not None:
+            if not hasattr(self, "_t_edges"):
+                self._t_edges = self.torch.from_numpy(
+                    synth.onehot_edges(cfg.n_cols, self.synth_shape["nnz"], cfg.seed or 0)).to(dev)
+            return synth.synth_onehot(rows, cfg.n_cols, self.synth_shape["nnz"], cfg.seed or 0, p, task, classes, dev,
+                                      edges=self._t_edges)
+        return synth.synth_gmm(rows, cfg.n_cols, cfg.seed or 0, p, task, dev, classes=classes)
+
     def _device_partition_fp32(self, p: int):
         torch = self.torch
         dev = self.ctx.device
@@ -240,11 +313,7 @@ class Engine:
         if self.data is None:
             if not cfg.synthetic:
                 raise ValueError("no dataset given and cfg.synthetic is off")
-            from .ops import synth
-            task = 1 if self.model.name == "linear" else 0
-            if self.mc:
-                raise ValueError("on-device synthetic data is binary; pass a dataset for multi-class models")
-            return synth.synth_gmm(spec.rows_per_part, cfg.n_cols, cfg.seed or 0, p, task, dev)
+            return self._synth_partition(spec.rows_per_part, p)
         y = torch.as_tensor(np.ascontiguousarray(self.data.labels(p)), dtype=torch.float32).to(dev)
         if self.sparse:
             idx = torch.from_numpy(np.ascontiguousarray(self.data.ell(p))).to(dev)
@@ -275,8 +344,8 @@ class Engine:
         dl[~np.isfinite(self.delays)] = np.uint64(NEVER_NS)
         self.t_delay = torch.from_numpy(dl.view(np.int64)).to(dev)
         self.t_eta = t(cfg.learning_rates(), torch.float64)
-        self.t_beta64 = t(pack_mc(self.beta0) if self.mc else self.beta0, torch.float64)
-        self.t_u64 = t(pack_mc(self.u0) if self.mc else self.u0, torch.float64)
+        self.t_beta64 = t(self._pack(self.beta0) if self.mc else self.beta0, torch.float64)
+        self.t_u64 = t(self._pack(self.u0) if self.mc else self.u0, torch.float64)
         self.t_betaset = torch.zeros((R, d), dtype=torch.float64, device=dev)
         self.t_timeset = torch.zeros(R, dtype=torch.float64, device=dev)
         self.t_wts = torch.full((R, n), -1.0, dtype=torch.float64, device=dev)
@@ -323,7 +392,17 @@ class Engine:
         if not self.on_gpu:
             return 0
         k = 0
-        if self.mc:
+        if self.mc and self.sparse:                               # batched 8 messages / 32 partitions per launch
+            nb = segs = 0
+            for q in range(self.n_jobs):
+                ns = self._jobs[q].n_segs
+                if nb and (nb == 8 or segs + ns > 32):
+                    k += 1
+                    nb = segs = 0
+                nb += 1
+                segs += ns
+            k += 1 if nb else 0
+        elif self.mc:
             # one launch per message for the one-pass kernels, else wait + 2 per partition + ship + flag
             one_pass = self.bf16 or _pad32(self.cfg.n_cols) <= 1024
             k = sum(1 if one_pass else 2 * self._jobs[q].n_segs + 3 for q in range(self.n_jobs))
@@ -499,8 +578,7 @@ class Engine:
         cpu = lambda t: t[:R].detach().cpu().numpy()
         betaset, u, beta = cpu(self.t_betaset), self.t_u64.cpu().numpy(), self.t_beta64.cpu().numpy()
         if self.mc:
-            dd, cc = self.cfg.n_cols, self.model.n_out
-            betaset, u, beta = unpack_mc(betaset, dd, cc), unpack_mc(u, dd, cc), unpack_mc(beta, dd, cc)
+            betaset, u, beta = self._unpack(betaset), self._unpack(u), self._unpack(beta)
         return oracle.RunResult(
             betaset=betaset, timeset=cpu(self.t_timeset), worker_timeset=cpu(self.t_wts),
             weights=cpu(self.t_weights), n_collected=cpu(self.t_ncol).astype(np.int64), u=u, beta=beta,
@@ -531,6 +609,8 @@ class Engine:
         R, d, C_ = betaset.shape
         n_parts = self._n_eval_parts() or spec.n_partitions
         Xt, yt = self._device_test()
+        if self.sparse:
+            return self._evaluate_gpu_mc_ell(betaset, n_parts, Xt, yt)
         tr, te = np.zeros(R), np.zeros(R)
         for i in range(R):
             Wp = torch.from_numpy(pack_mc(betaset[i]).astype(np.float32)).to(dev)
@@ -552,6 +632,44 @@ class Engine:
             _, M = mops.eval_tc(Xt, Wi, None, d=d, want_margins=True)
             acc[i] = float((M[:, :C_].argmax(dim=1) == yt.long()).float().mean().item())
         return results.Evaluation(tr, te, None, acc)
+
+    def _evaluate_gpu_mc_ell(self, betaset: np.ndarray, n_parts: int, Xt, yt):
+        """One-hot features, C-column model: the ELL margin kernel evaluates the C columns of up to 32 / C iterates
+        per pass over the indices; cross-entropy and accuracy are reductions of the logits on the device, one host
+        read per quantity at the end."""
+        from . import results
+        from .ops import metrics as mops
+        torch = self.torch
+        dev = self.ctx.device
+        R, d, C_ = betaset.shape
+        per = max(1, 32 // C_)
+        tr = torch.zeros(R, dtype=torch.float64, device=dev)
+        te = torch.zeros(R, dtype=torch.float64, device=dev)
+        acc = torch.zeros(R, dtype=torch.float64, device=dev)
+        rows_tr = 0
+
+        def stats(idx, y, Bt, n_it):
+            P = mops.margins_ell(idx, Bt)[:, :n_it * C_].reshape(idx.shape[0], n_it, C_).double()
+            yl = y.long()
+            ce = torch.logsumexp(P, dim=2) - P.gather(2, yl[:, None, None].expand(-1, n_it, 1)).squeeze(2)
+            hit = (P.argmax(dim=2) == yl[:, None]).double()
+            return ce.sum(dim=0), hit.sum(dim=0)
+
+        for i0 in range(0, R, per):
+            n_it = min(per, R - i0)
+            Bt = torch.zeros((n_it * C_, _pad32(d)), dtype=torch.float32, device=dev)
+            Wb = torch.from_numpy(np.ascontiguousarray(np.swapaxes(betaset[i0:i0 + n_it], 1, 2))).to(dev)   # [n_it, C, d]
+            Bt[:, :d] = Wb.reshape(n_it * C_, d).float()
+            for p in range(n_parts):
+                Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
+                ce, _ = stats(Xp, yp, Bt, n_it)
+                tr[i0:i0 + n_it] += ce
+                if i0 == 0:
+                    rows_tr += Xp.shape[0]
+            ce, hit = stats(Xt, yt, Bt, n_it)
+            te[i0:i0 + n_it] = ce / Xt.shape[0]
+            acc[i0:i0 + n_it] = hit / Xt.shape[0]
+        return results.Evaluation((tr / rows_tr).cpu().numpy(), te.cpu().numpy(), None, acc.cpu().numpy())
 
     def _evaluate_gpu(self, betaset: np.ndarray):
         from . import results
@@ -605,10 +723,8 @@ class Engine:
         dev = self.ctx.device
         cfg = self.cfg
         if self.data is None:
-            from .ops import synth
-            task = 1 if self.model.name == "linear" else 0
             n_test = max(1, int(0.2 * cfg.n_rows))                         # generate_data.py:40
-            return synth.synth_gmm(n_test, cfg.n_cols, cfg.seed or 0, (1 << 40), task, dev)
+            return self._synth_partition(n_test, (1 << 40))
         yt = torch.as_tensor(np.ascontiguousarray(self.data.y_test), dtype=torch.float32).to(dev)
         if self.sparse:
             return torch.from_numpy(np.ascontiguousarray(self.data.ell(test=True))).to(dev), yt
@@ -628,8 +744,7 @@ class Engine:
         if self.on_gpu:
             beta, u = self.t_beta64.cpu().numpy(), self.t_u64.cpu().numpy()
             if self.mc:
-                beta, u = (unpack_mc(beta, self.cfg.n_cols, self.model.n_out),
-                           unpack_mc(u, self.cfg.n_cols, self.model.n_out))
+                beta, u = self._unpack(beta), self._unpack(u)
         else:
             beta, u = self.result.beta, self.result.u
         np.savez(path, next_round=next_round, beta=beta, u=u,

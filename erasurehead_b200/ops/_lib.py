@@ -139,6 +139,9 @@ def _declare(lib):
         "eh_grad_ell_scratch_bytes": (sz, [i32]),
         "eh_grad_ell": (i32, [P(GradEllJob), vp, sz, vp]),
         "eh_grad_ell_multi": (i32, [P(GradEllJob), i32, vp, sz, vp]),
+        "eh_grad_ell_mc_padded_classes": (i32, []),
+        "eh_grad_ell_mc_scratch_bytes": (sz, [i32]),
+        "eh_grad_ell_mc_multi": (i32, [P(GradEllJob), i32, i32, vp, sz, vp]),
         "eh_decoder_scratch_bytes": (sz, []),
         "eh_decoder_ctas": (i32, [i32]),
         "eh_set_reserved_sms": (i32, [i32]),
@@ -156,7 +159,8 @@ def _declare(lib):
         "eh_loss_columns": (i32, [vp, vp, i64, i32, i32, vp, vp]),
         "eh_auc": (i32, [vp, vp, i64, vp, vp, sz, vp]),
         "eh_auc_scratch_bytes": (sz, [i64]),
-        "eh_synth_gmm": (i32, [vp, vp, i64, i32, i32, u64, u64, i32, vp]),
+        "eh_synth_gmm": (i32, [vp, vp, i64, i32, i32, u64, u64, i32, i32, vp]),
+        "eh_synth_onehot": (i32, [vp, vp, i64, i32, i32, vp, u64, u64, i32, i32, vp]),
         "eh_onehot_assemble": (i32, [vp, vp, i64, i32, vp, vp]),
         "eh_pair_codes": (i32, [vp, i64, i32, vp, i32, vp, vp, vp]),
         "eh_code_cyclic": (i32, [vp, i32, i32, vp, vp]),

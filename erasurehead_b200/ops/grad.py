@@ -140,3 +140,17 @@ def grad_ell(idx, y, beta: torch.Tensor, coeff: Sequence[float] = (1.0,), model:
     job = make_ell_job(idxs, ys, beta.data_ptr(), out.data_ptr(), d, list(coeff), model, bias_col)
     launch_ell(job, scratch)
     return out
+
+
+def grad_ell_mc(idx, y, W: torch.Tensor, classes: int, coeff: Sequence[float] = (1.0,), model: int = 2) -> torch.Tensor:
+    """Standalone multi-column gradient on one-hot features: ``W`` and the result are ``[d, 8]`` float32
+    (column-major, ``classes <= 8`` used; csrc/grad_ell_mc.cu).  Labels: class ids (model 2) or +-1 (model 3)."""
+    idxs, ys = _aslist(idx), _aslist(y)
+    d = W.shape[0]
+    assert W.dtype == torch.float32 and W.is_contiguous() and W.shape[1] == lib().eh_grad_ell_mc_padded_classes()
+    out = torch.empty_like(W)
+    sc = Scratch(lib().eh_grad_ell_mc_scratch_bytes(d), idxs[0].device)
+    job = make_ell_job(idxs, ys, W.data_ptr(), out.data_ptr(), d, list(coeff), model, -1)
+    _lib.check(lib().eh_grad_ell_mc_multi(C.byref(job), 1, int(classes), sc.ptr(), sc.nbytes, _lib.stream_ptr()),
+               "eh_grad_ell_mc_multi")
+    return out

@@ -152,6 +152,20 @@ int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_byte
  * message); otherwise one launch per message. */
 int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes, void* stream);
 
+/* Multi-column model on one-hot ELL features: softmax regression with C <= 8 classes (model 2, labels
+ * 0..C-1) or C independent logistic columns (model 3, labels +-1) -- "Covertype-shaped multi-class" at
+ * the one-hot shape 396112 x 15509 (BASELINE.json config 5; the reference binarises Covertype,
+ * arrange_real_data.py:154-156, so the model has no reference counterpart).  Jobs are eh_grad_ell_job
+ * with d_beta / d_out in COLUMN-major layout W[d][8] (eh_grad_ell_mc_padded_classes() floats per
+ * feature: one 32-byte sector) -- a flat vector of 8 d floats for the decoder; bias_col is ignored.
+ * Up to 8 messages of one shape per launch (CTA ranges per message, one accumulation vector each in
+ * scratch >= eh_grad_ell_mc_scratch_bytes(d)); scatter by 16-byte L2 reductions with a per-lane
+ * run-length cache (csrc/grad_ell_mc.cu). */
+int eh_grad_ell_mc_padded_classes(void);
+size_t eh_grad_ell_mc_scratch_bytes(int d);
+int eh_grad_ell_mc_multi(const eh_grad_ell_job* jobs, int n_jobs, int classes, void* d_scratch, size_t scratch_bytes,
+                         void* stream);
+
 /* Multi-column models on the tensor cores (tcgen05.mma kind::tf32 for both products): softmax
  * regression with C classes (model 2, labels 0..C-1) and C independent logistic columns on the
  * same data (model 3, labels +-1).  Parameters / gradients use the class-major layout
@@ -266,7 +280,7 @@ typedef struct eh_worker_job {
     int32_t  worker;                 /* global worker id (slot row on the root) */
     int32_t  msg;                    /* EH_MSG_CODED / EH_MSG_PRIVATE */
     int32_t  sparse;                 /* 0: dense fp32 rows, 1: one-hot ELL, 2: dense multi-column (tensor cores), 3: dense bf16 rows,
-                                        4: dense multi-column with bf16 rows (d <= 640) */
+                                        4: dense multi-column with bf16 rows (d <= 640), 5: one-hot ELL multi-column (<= 8 classes) */
     int32_t  model;
     int32_t  n_segs, rows_per_seg;
     int32_t  d, ld_or_nnz;           /* dense: row stride; ELL: ones per row */
@@ -336,8 +350,16 @@ size_t eh_auc_scratch_bytes(int64_t n);
  * ---------------------------------------------------------------------------------------- */
 /* GMM features + logistic labels, counter-based (Philox) so that any (partition,row,col) is
  * reproducible on any GPU (generate_data.py:23-45, util.py:39-47). */
+/* task 0: labels +-1 ~ Bernoulli(sigmoid(x.beta_star)); 1: real targets (x.beta_star) / sqrt(d) + noise; 2: class ids
+ * 0..classes-1 = argmax_k(0.3 x.w_k + Gumbel), w_k in {-1,+1}^d (classes <= 8; multi-class extension). */
 int eh_synth_gmm(float* d_X, float* d_y, int64_t rows, int d, int ld, uint64_t seed,
-                 uint64_t partition, int task, void* stream);
+                 uint64_t partition, int task, int classes, void* stream);
+/* One-hot ELL data of a named dataset's shape (arrange_real_data.py:41-64,151-178,211-221 builds this from
+ * the real files): idx[rows, nnz] int32 with one feature per categorical block [d_edges[f], d_edges[f+1])
+ * for f < nnz-1 (heavy-tailed level popularity) and the always-on bias feature d-1 last; labels as above
+ * from hidden N(0, 0.5^2) parameters per feature (and class). */
+int eh_synth_onehot(int32_t* d_idx, float* d_y, int64_t rows, int d, int nnz, const int32_t* d_edges,
+                    uint64_t seed, uint64_t partition, int task, int classes, void* stream);
 /* Cyclic-MDS code B from the parity matrix H (util.py:64-83): one warp per row. */
 int eh_code_cyclic(const double* d_H, int n, int s, double* d_B, void* stream);
 /* Decode table A (util.py:85-103): one warp per straggler pattern. */

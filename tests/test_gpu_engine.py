@@ -324,3 +324,42 @@ def test_arrival_is_completion_plus_delay_and_decoder_overlaps_compute():
     assert res2.timeset[0] > 3.5 * job
     assert np.allclose(res2.betaset, res.betaset, atol=1e-6)     # 147 vs 148 gradient CTAs: other summation order
     eng2.close()
+
+
+@pytest.mark.parametrize("scheme,kw", [("approx", dict(s=1, k=5)), ("coded", dict(s=2, seed=3))])
+def test_engine_softmax_on_onehot_features_matches_oracle(scheme, kw):
+    """Multi-class model on one-hot (ELL) features -- 'Covertype-shaped multi-class' -- against the oracle."""
+    cfg = mk(scheme, rows=8 * 300, d=900, model="softmax", classes=7, **kw)
+    data = generate_onehot(cfg.n_rows, cfg.n_cols, 12, cfg.n_partitions, seed=4, task="softmax", classes=7)
+    dl = spaced_delays(cfg.rounds, cfg.n_workers, seed=6)
+    eng = Engine(cfg, data, delays=dl)
+    assert eng.on_gpu and eng.sparse and eng.mc
+    res = eng.run()
+    ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0)
+    assert res.betaset.shape == ref.betaset.shape == (cfg.rounds, 900, 7)
+    scale = max(1.0, np.abs(ref.betaset).max())
+    assert np.abs(res.betaset - ref.betaset).max() <= 5e-4 * scale
+    assert np.array_equal(res.worker_timeset >= 0, ref.worker_timeset >= 0)
+    ev = eng.evaluate(res)
+    from erasurehead_b200 import results
+    evh = results.evaluate_host(eng.model, data, res.betaset)
+    assert np.allclose(ev.training_loss, evh.training_loss, rtol=1e-4, atol=1e-5)
+    assert np.allclose(ev.testing_loss, evh.testing_loss, rtol=1e-4, atol=1e-5)
+    eng.close()
+
+
+@pytest.mark.parametrize("model,classes", [("logistic", 1), ("softmax", 7)])
+def test_engine_runs_on_device_generated_onehot_shapes(model, classes):
+    """--synthetic with is_real=1: one-hot data of the Covertype shape generated on the GPU (no host data),
+    binary and 7-class; the loss must go down."""
+    n, s, k = 6, 2, 3
+    ic, pp, cv = triple_from_scheme("approx")
+    cfg = RunConfig(n + 1, 6 * 4000, 15509, "", 1, "covtype", ic, s, pp, cv, k, 0, "AGD", rounds=12, synthetic=True,
+                    seed=2, model=model, classes=classes, init="zeros", eta0=2.0)
+    eng = Engine(cfg, None)
+    assert eng.sparse and eng.synth_shape == {"nnz": 55}
+    res = eng.run()
+    ev = eng.evaluate(res)
+    assert np.all(np.isfinite(res.betaset))
+    assert ev.training_loss[-1] < ev.training_loss[0]
+    eng.close()

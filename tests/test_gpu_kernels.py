@@ -420,3 +420,65 @@ def test_kernels_on_a_second_device_in_one_process():
         assert torch.allclose(outs[0], outs[1], rtol=1e-5, atol=1e-5)
     finally:
         torch.cuda.set_device(0)
+
+
+@pytest.mark.parametrize("model,C_", [(2, 7), (2, 3), (3, 5)])
+def test_grad_ell_mc_matches_reference(model, C_):
+    """Multi-column gradient on one-hot features (column-major W[d][8]) against float64 torch."""
+    from erasurehead_b200.data import generate_onehot
+    from erasurehead_b200.ops import grad
+    d, nnz, rpp = 6000, 23, 2500
+    ds = generate_onehot(3 * rpp, d, nnz, 3, seed=6, task="softmax", classes=C_)
+    idxs = [torch.from_numpy(ds.ell(p)).to(DEV) for p in range(3)]
+    if model == 2:
+        ys = [torch.tensor(ds.labels(p), dtype=torch.float32, device=DEV) for p in range(3)]
+    else:
+        ys = [torch.where(torch.rand(rpp, device=DEV) > 0.5, 1.0, -1.0) for _ in range(3)]
+    cf = [1.0, -2.5, 0.25]
+    W = torch.zeros(d, 8, device=DEV)
+    W[:, :C_] = torch.randn(d, C_, device=DEV) * 0.3
+    G = grad.grad_ell_mc(idxs, ys, W, C_, coeff=cf, model=model)
+    want = torch.zeros(d, C_, dtype=torch.float64, device=DEV)
+    for i, y, c in zip(idxs, ys, cf):
+        X = torch.sparse_csr_tensor(torch.arange(0, i.numel() + 1, nnz, device=DEV), i.reshape(-1).long(),
+                                    torch.ones(i.numel(), dtype=torch.float64, device=DEV), size=(i.shape[0], d))
+        P = X @ W[:, :C_].double()
+        if model == 2:
+            R = torch.softmax(P, dim=1)
+            R[torch.arange(len(y)), y.long()] -= 1.0
+        else:
+            R = -y.double()[:, None] / (torch.exp(P * y.double()[:, None]) + 1)
+        want += c * (X.t().to_sparse_csr() @ R)
+    assert (G[:, :C_].double() - want).abs().max().item() <= 5e-4 * max(1.0, want.abs().max().item())
+    assert G[:, C_:].abs().max().item() == 0.0
+
+
+def test_synth_onehot_and_multiclass_labels_on_device():
+    """Device generators of the named dataset shapes (K14): fixed ones per row inside their blocks, bias last,
+    reproducible per (seed, partition), label distributions sane; dense multi-class labels."""
+    from erasurehead_b200.ops import synth
+    d, nnz, rows = 15509, 55, 20000
+    edges = synth.onehot_edges(d, nnz, 3)
+    idx, y = synth.synth_onehot(rows, d, nnz, 3, 7, task=0)
+    idx2, y2 = synth.synth_onehot(rows, d, nnz, 3, 7, task=0)
+    assert torch.equal(idx, idx2) and torch.equal(y, y2)
+    idx3, _ = synth.synth_onehot(rows, d, nnz, 3, 8, task=0)
+    assert not torch.equal(idx, idx3)
+    e = torch.from_numpy(edges).to(DEV)
+    assert torch.all(idx[:, -1] == d - 1)
+    assert torch.all(idx[:, :-1] >= e[:-1][None, :]) and torch.all(idx[:, :-1] < e[1:][None, :])
+    assert set(y.unique().tolist()) == {-1.0, 1.0} and 0.1 < (y > 0).float().mean().item() < 0.9
+    # heavy-tailed popularity: the most frequent level of a wide block takes a large share of the rows
+    wide = int(np.argmax(np.diff(edges)))
+    top = torch.bincount(idx[:, wide].long() - int(edges[wide])).max().item() / rows
+    assert 0.1 < top < 0.6
+    _, yl = synth.synth_onehot(rows, d, nnz, 3, 7, task=1)
+    assert yl.std().item() > 0.05
+    _, yc = synth.synth_onehot(rows, d, nnz, 3, 7, task=2, classes=7)
+    cnt = torch.bincount(yc.long(), minlength=7)
+    assert cnt.numel() == 7 and cnt.min().item() > rows // 70
+    Xd, yd = synth.synth_gmm(4096, 512, seed=5, partition=1, task=2, classes=5)
+    cd = torch.bincount(yd.long(), minlength=5)
+    assert cd.numel() == 5 and cd.min().item() > 4096 // 50
+    X0, _ = synth.synth_gmm(4096, 512, seed=5, partition=1, task=0)
+    assert torch.equal(Xd, X0)              # the features do not depend on the label task
