@@ -67,11 +67,18 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
     __shared__ float s_val[GE_TABLE];
     for (int i = threadIdx.x; i < GE_TABLE; i += GE_THREADS) { s_tag[i] = -1; s_val[i] = 0.f; }
     const int tid = threadIdx.x, lane = tid & 31;
-    const int gthreads = gridDim.x * GE_THREADS;
-    const int gtid = blockIdx.x * GE_THREADS + tid;
+    // which batched message this CTA works for: message jb owns CTAs [job_cta0[jb], job_cta0[jb+1]), its own
+    // accumulation vector in scratch and its own destination / arrival record
+    int jb = 0;
+    while (jb + 1 < p.n_jobs && (int)blockIdx.x >= p.job_cta0[jb + 1]) ++jb;
+    const int b0 = p.job_cta0[jb], Gj = p.job_cta0[jb + 1] - b0, seg0 = p.job_seg0[jb];
+    const int gthreads = Gj * GE_THREADS;
+    const int gtid = ((int)blockIdx.x - b0) * GE_THREADS + tid;
+    float* gacc = p.gacc + (size_t)jb * (size_t)((p.d + 31) & ~31);
+    const long long job_rows = (long long)p.rows_per_seg * p.job_nsegs[jb];
 
     // zero the accumulator (does not depend on this round's parameters)
-    for (int c = gtid; c < p.d; c += gthreads) p.gacc[c] = 0.f;
+    for (int c = gtid; c < p.d; c += gthreads) gacc[c] = 0.f;
 
     if (tid == 0) {
         uint32_t code = GE_GO;
@@ -108,8 +115,8 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
     const long long gwarp = gtid >> 5;
     const long long nwarps = gthreads >> 5;
     float bias_acc = 0.f;
-    for (long long row = gwarp; row < p.rows; row += nwarps) {
-        const int sg = (int)(row / p.rows_per_seg);
+    for (long long row = gwarp; row < job_rows; row += nwarps) {
+        const int sg = seg0 + (int)(row / p.rows_per_seg);
         const int lr = (int)(row % p.rows_per_seg);
         const int32_t* ri = p.seg_idx[sg] + (size_t)lr * p.nnz;
         float s = 0.f;
@@ -128,24 +135,27 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
                     t = (old == -1) ? c : old;
                 }
                 if (t == c) atomicAdd(&s_val[slot], rs);
-                else atomicAdd(p.gacc + c, rs);
+                else atomicAdd(gacc + c, rs);
             }
         }
     }
     if (p.bias_col >= 0) {
         bias_acc = warp_sum(bias_acc);
-        if (lane == 0 && bias_acc != 0.f) atomicAdd(p.gacc + p.bias_col, bias_acc);
+        if (lane == 0 && bias_acc != 0.f) atomicAdd(gacc + p.bias_col, bias_acc);
     }
     __syncthreads();
     for (int i = tid; i < GE_TABLE; i += GE_THREADS) {
         const int t = s_tag[i];
         const float v = s_val[i];
-        if (t >= 0 && v != 0.f) atomicAdd(p.gacc + t, v);
+        if (t >= 0 && v != 0.f) atomicAdd(gacc + t, v);
     }
 
     grid_barrier(&p.hdr->barrier, gen);
 
-    for (int c = gtid; c < p.d; c += gthreads) p.out[c] = __ldcg(p.gacc + c);
+    {
+        float* out = p.job_out[jb];
+        for (int c = gtid; c < p.d; c += gthreads) out[c] = __ldcg(gacc + c);
+    }
 
     __syncthreads();
     if (tid == 0) {
@@ -154,9 +164,11 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
         if (old == gridDim.x - 1) {
             p.hdr->barrier = 0;
             p.hdr->done = 0;
-            if (p.flag) st_arrival_time(p.flag);
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_arrival_time(p.job_flag[j]);
             __threadfence_system();
-            if (p.flag) st_release_sys(p.flag, p.stamp);
+            for (int j = 0; j < p.n_jobs; ++j)
+                if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);
         }
     }
 }
@@ -570,7 +582,8 @@ constexpr size_t GES_SMEM_LIMIT = 224 * 1024;
 }  // namespace eh
 
 extern "C" size_t eh_grad_ell_scratch_bytes(int d) {
-    size_t b = sizeof(eh::EllScratchHdr) + (size_t)(d + 32) * sizeof(float);
+    // global-atomic variant: one accumulation vector per batched message
+    size_t b = sizeof(eh::EllScratchHdr) + (size_t)eh::GE_MAX_JOBS * (size_t)((d + 31) / 32 * 32 + 32) * sizeof(float);
     if ((size_t)(d + 4) * sizeof(float) <= eh::GES_SMEM_LIMIT) {      // shared-memory variant: per-CTA partials
         int sm = eh::dev_info().sm_count;
         if (sm <= 0) sm = 160;
@@ -579,9 +592,9 @@ extern "C" size_t eh_grad_ell_scratch_bytes(int d) {
     return b;
 }
 
-// Up to GE_MAX_JOBS messages of one shape in ONE launch of the shared-memory variant (CTA ranges per message,
-// proportional to their partition counts); feature spaces too large for shared memory fall back to one
-// global-atomic launch per message.
+// Up to GE_MAX_JOBS messages of one shape in ONE launch (CTA ranges per message, proportional to their partition
+// counts) -- in the shared-memory variants with per-CTA partial gradients, in the global-atomic variant (feature
+// spaces too large for shared memory, e.g. the Amazon shape) with one accumulation vector per message in scratch.
 extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes,
                                  void* stream) {
     using namespace eh;
@@ -594,13 +607,6 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
     const DevInfo& di = dev_info();
     const size_t acc_bytes = (size_t)((j->d + 3) & ~3) * sizeof(float);
     const bool smem_variant = acc_bytes <= GES_SMEM_LIMIT && getenv("EH_ELL_GLOBAL") == nullptr;
-    if (!smem_variant && n_jobs > 1) {
-        for (int q = 0; q < n_jobs; ++q) {
-            const int rc = eh_grad_ell_multi(&jobs[q], 1, d_scratch, scratch_bytes, stream);
-            if (rc) return rc;
-        }
-        return EH_OK;
-    }
     EllParams p;
     memset(&p, 0, sizeof(p));
     int nseg = 0;
@@ -675,12 +681,24 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
     EH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, grad_ell_kernel, GE_THREADS, 0));
     if (occ > 2) occ = 2;                       // fewer, larger CTAs: fewer tables to flush
     if (occ < 1) occ = 1;
-    long long want = (p.rows * 32 + GE_THREADS - 1) / GE_THREADS;      // one warp per row
-    long long cols = ((long long)j->d + GE_THREADS - 1) / GE_THREADS;
+    // CTAs per message in proportion to its partitions: one warp per row, and enough threads to zero / ship d columns
+    const long long total_rows = (long long)j->rows_per_seg * nseg;
+    long long want = (total_rows * 32 + GE_THREADS - 1) / GE_THREADS;
+    const long long cols = (((long long)j->d + GE_THREADS - 1) / GE_THREADS) * n_jobs / 4;      // ~4 columns per thread
     if (cols > want) want = cols;
     long long grid = (long long)worker_sms() * occ;
     if (grid > want) grid = want;
-    if (grid < 1) grid = 1;
+    if (grid < n_jobs) grid = n_jobs;
+    {
+        const long long spare = grid - n_jobs;
+        int used = 0;
+        p.job_cta0[0] = 0;
+        for (int q = 0; q < n_jobs; ++q) {
+            used += 1 + (int)(spare * p.job_nsegs[q] / nseg);
+            p.job_cta0[q + 1] = used;
+        }
+        grid = used;
+    }
     void* args[] = {(void*)&p};
     { int lrc = launch_grid_sync((const void*)grad_ell_kernel, dim3((unsigned)grid), dim3(GE_THREADS), args, 0, (cudaStream_t)stream); if (lrc) return lrc; }
     return EH_OK;

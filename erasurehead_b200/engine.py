@@ -406,19 +406,16 @@ class Engine:
             # one launch per message for the one-pass kernels, else wait + 2 per partition + ship + flag
             one_pass = self.bf16 or _pad32(self.cfg.n_cols) <= 1024
             k = sum(1 if one_pass else 2 * self._jobs[q].n_segs + 3 for q in range(self.n_jobs))
-        elif self.sparse:
-            if (self.cfg.n_cols + 4) * 4 > 224 * 1024:            # gradient not in shared memory: one launch per message
-                k = self.n_jobs
-            else:                                                 # batched 8 messages / 32 partitions per launch
-                nb = segs = 0
-                for q in range(self.n_jobs):
-                    ns = self._jobs[q].n_segs
-                    if nb and (nb == 8 or segs + ns > 32):
-                        k += 1
-                        nb = segs = 0
-                    nb += 1
-                    segs += ns
-                k += 1 if nb else 0
+        elif self.sparse:                                          # batched 8 messages / 32 partitions per launch
+            nb = segs = 0
+            for q in range(self.n_jobs):
+                ns = self._jobs[q].n_segs
+                if nb and (nb == 8 or segs + ns > 32):
+                    k += 1
+                    nb = segs = 0
+                nb += 1
+                segs += ns
+            k += 1 if nb else 0
         else:
             nb = segs = 0
             big_prev = False
