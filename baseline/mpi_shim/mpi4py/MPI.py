@@ -106,6 +106,8 @@ def _send(dest, tag, payload):
                     break
                 except OSError:
                     time.sleep(0.05)
+            if s is None:
+                raise RuntimeError("mpi shim: rank %d cannot reach rank %d on port %d" % (_RANK, dest, _PORT0 + dest))
             s.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
             _out[dest] = s
         s.sendall(struct.pack("<iiq", _RANK, tag, len(payload)) + payload)

@@ -18,11 +18,31 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.path.join(HERE, "_ref")
 
 
+def _free_port_range(n):
+    """A base port such that port0 .. port0+n-1 can all be bound right now (one listening port per rank)."""
+    import socket
+    for _ in range(200):
+        port0 = 30000 + random.randint(0, 20000)
+        socks = []
+        try:
+            for r in range(n):
+                sk = socket.socket()
+                sk.bind(("127.0.0.1", port0 + r))
+                socks.append(sk)
+            return port0
+        except OSError:
+            continue
+        finally:
+            for sk in socks:
+                sk.close()
+    raise RuntimeError("no free range of %d local ports found" % n)
+
+
 def launch(n, rest, stdout=None, env_extra=None):
     """Start the ranks; returns the list of Popen objects (rank 0 first)."""
     if not os.path.exists(os.path.join(REF, "main.py")):
         subprocess.check_call(["bash", os.path.join(HERE, "install_ref.sh")])
-    port0 = 30000 + random.randint(0, 20000)
+    port0 = _free_port_range(n)
     procs = []
     for r in range(n):
         env = dict(os.environ, EH_MPI_RANK=str(r), EH_MPI_SIZE=str(n), EH_MPI_PORT0=str(port0),

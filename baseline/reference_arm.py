@@ -113,14 +113,23 @@ def run_main(n_procs, args13, timeout):
     procs = mpirun_shim.launch(n_procs, ["main.py"] + [str(a) for a in args13], stdout=log)
     deadline = t0 + timeout
     rc = 0
-    try:
-        for p in procs:
-            rc |= p.wait(timeout=max(1.0, deadline - time.time()))
-    except subprocess.TimeoutExpired:
-        for p in procs:
-            if p.poll() is None:
-                p.kill()
-        rc = -9
+    # a rank that dies (e.g. rank 0 raising in its evaluation epilogue) leaves the others in a barrier for ever:
+    # poll, and stop everything as soon as one rank fails or the time is up
+    while True:
+        codes = [p.poll() for p in procs]
+        if all(c is not None for c in codes):
+            rc = max((abs(c) for c in codes), default=0)
+            break
+        if any(c not in (None, 0) for c in codes) or time.time() > deadline:
+            time.sleep(1.0)
+            for p in procs:
+                if p.poll() is None:
+                    p.kill()
+            for p in procs:
+                p.wait()
+            rc = next((abs(c) for c in codes if c not in (None, 0)), 9)
+            break
+        time.sleep(0.05)
     wall = time.time() - t0
     log.flush()
     log.seek(0)
