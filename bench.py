@@ -26,6 +26,9 @@ Besides the headline the JSON line carries (each skippable, see the --no-* flags
   matched         the headline at the reference arm's size (--ref-rows rows per partition) without delays
                   and with the reference's Exp(0.5 s) delays: the same-configuration counterpart of
                   ``bench.py --impl reference``
+  abandon         the headline with --abandon: workers whose round has been decided stop streaming (a straggler's
+                  compute is skipped, not only its message); fewer rows are read per round, so this is reported
+                  next to the headline, never as the headline
   covtype         AGC at the reference launcher's real-data configuration (30 workers, n_collect 15,
                   one-hot 396112 x 15509, AGD, no injected delay) -- same data generator and seed as
                   the reference arm's ``covtype`` block
@@ -377,6 +380,15 @@ def main():
             guarded("parity", lambda: block_parity(ctx, args, N))
         if not args.no_matched:
             guarded("matched", lambda: block_matched(ctx, args, N, K, W))
+        if not args.no_matched:
+            def abandon():
+                c2, _, _, _ = headline_cfg(args, N, args.rows, 2 * (W + K) + 2, args.delay_scale, abandon=True)
+                e2 = Engine(c2, None, ctx=ctx)
+                ams, _, _ = measure(ctx, e2, K, W, e2e=False)
+                release(e2)
+                return {"ms_per_step": ams / K, "value": n_rows * K / (ams * 1e-3), "unit": "samples/s (rows of decided "
+                        "rounds that were not read still count: compare ms_per_step, not this, with the headline)"}
+            guarded("abandon", abandon)
         if not args.no_covtype:
             guarded("covtype", lambda: block_covtype(ctx, args, K, W))
     if ctx.is_root:

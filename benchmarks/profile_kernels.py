@@ -61,6 +61,17 @@ def mc_fused(rows, d, C_, reps=2, bf16=False):
     assert torch.isfinite(G).all()
 
 
+def ell_mc(rows, d, nnz, C_, reps=2):
+    from erasurehead_b200.ops import grad, synth
+    idx, y = synth.synth_onehot(rows, d, nnz, 1, 0, task=2, classes=C_)
+    W = torch.zeros(d, 8, device="cuda")
+    W[:, :C_] = torch.randn(d, C_, device="cuda") * 0.1
+    for _ in range(reps):
+        G = grad.grad_ell_mc(idx, y, W, C_)
+    torch.cuda.synchronize()
+    assert torch.isfinite(G).all()
+
+
 def rounds():
     from erasurehead_b200 import Engine, RunConfig, triple_from_scheme
     ic, p, cv = triple_from_scheme("coded")
@@ -94,6 +105,8 @@ if __name__ == "__main__":
             mc_fused(4194304, 256, 16, bf16=True)
         elif w == "mc_cluster":
             mc_fused(524288, 1024, 16)
+        elif w == "ell_mc":
+            ell_mc(396112, 15509, 55, 7)
         elif w == "round":
             rounds()
         print("ok", w, flush=True)

@@ -407,6 +407,10 @@ extern "C" int eh_decoder_publish(const eh_decoder_desc* D, int round, void* str
     if (rc) return rc;
     int grid = (D->d_pad / 4 + 255) / 256;
     if (grid > 1024) grid = 1024;
+    // load the round kernel now: with lazy module loading its first launch would otherwise wait for the gradient
+    // kernels that are already running on the other stream, i.e. the first round would not overlap
+    cudaFuncAttributes fa;
+    EH_CUDA(cudaFuncGetAttributes(&fa, decoder_round_kernel));
     publish_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*D, round);
     publish_flag_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*D, round);
     EH_CUDA(cudaGetLastError());

@@ -84,6 +84,7 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.ld = wj.ld_or_nnz;
                 j.model = wj.model; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
                 j.x_bf16 = (wj.sparse == 3);
+                j.abandon = plan->abandon;
                 // batching pays for latency-bound messages; a bandwidth-bound message (> 16 MB of X) gets
                 // its own launch so that it ships as soon as it is done instead of with the slowest one
                 const size_t job_bytes = (size_t)j.n_segs * j.rows_per_seg * j.ld * (j.x_bf16 ? 2 : 4);

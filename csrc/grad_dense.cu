@@ -57,11 +57,14 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
     uint64_t* empty = full + GD_MAX_STAGES;
     float* red = reinterpret_cast<float*>(empty + GD_MAX_STAGES);      // [2][RB][8], 16-byte aligned
     __shared__ uint32_t s_decision;
+    __shared__ long long s_stop_store;
+    volatile long long* s_stop = &s_stop_store;
 
     const JobView jv = job_of_cta(p);
     const long long my_steps = (jv.bl < jv.n_steps) ? (jv.n_steps - jv.bl + jv.Gj - 1) / jv.Gj : 0;
 
     if (tid == 0) {
+        s_stop_store = NO_STOP;
         for (int s = 0; s < p.n_stages; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], GD_CONSUMER_WARPS);
@@ -108,6 +111,10 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
                 const int st = (int)(k % p.n_stages);
                 const uint32_t use = (uint32_t)(k / p.n_stages);      // >= 1 here
                 mbar_wait_backoff(&empty[st], (use - 1) & 1);
+                if (p.abandon && (k & 7) == 0 && round_is_over(p)) {
+                    producer_abandon(p, s_stop, k, &full[st]);
+                    break;
+                }
                 issue(k);
             }
         }
@@ -144,7 +151,9 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_kernel(const GradPar
             float yv[RB];
 #pragma unroll
             for (int r = 0; r < RB; ++r) yv[r] = (r < nr) ? __ldg(ys + r) : 0.f;
+            if (p.abandon && k >= *s_stop) break;
             mbar_wait(&full[st], phase);
+            if (p.abandon && k >= *s_stop) break;
             const uint4* tile = reinterpret_cast<const uint4*>(stages + (size_t)st * stage_bytes);
             float x[RB][DV][E];
             float dot[RB];
@@ -284,6 +293,7 @@ static int fill_and_launch(const eh_grad_job* jobs, int n_jobs, void* d_scratch,
     GradParams p;
     memset(&p, 0, sizeof(p));
     p.x_bf16 = j0->x_bf16 ? 1 : 0;
+    p.abandon = (j0->abandon && j0->d_beta_flag) ? 1 : 0;
     int nseg = 0;
     for (int q = 0; q < n_jobs; ++q) {
         const eh_grad_job* j = &jobs[q];

@@ -18,9 +18,10 @@ struct GradScratchHdr {          // first 512 bytes of the scratch buffer
     alignas(128) uint32_t barrier;     // device-wide barrier ticket
     alignas(128) uint32_t done;        // final ticket
     alignas(128) uint32_t decision;    // (seq << 2) | code, written by CTA 0
-    alignas(128) uint32_t pad;
+    alignas(128) uint32_t aborted;     // set by any CTA that abandoned the round (GradParams::abandon); reset by the last CTA
 };
 constexpr uint32_t DEC_GO = 1, DEC_SKIP = 2;
+constexpr long long NO_STOP = 0x7fffffffffffffffll;
 
 struct GradParams {
     const void* seg_X[GD_TOTAL_SEGS];   // fp32 rows, or bf16 rows when x_bf16
@@ -37,6 +38,7 @@ struct GradParams {
     int job_nsegs[GD_MAX_JOBS];
     int n_jobs;
     int x_bf16;
+    int abandon;                 // watch beta_flag while streaming and stop once the round is over
     const uint32_t* beta_flag;
     uint32_t* err;
     GradScratchHdr* hdr;
@@ -89,8 +91,10 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
     float* out = p.job_out[jv.jb];
     uint32_t gen = 0;
     grid_barrier(&p.hdr->barrier, gen);
+    // a CTA that saw the round end while streaming raised hdr->aborted before the barrier: nothing is shipped
+    const bool aborted = p.abandon && ld_acquire_gpu(&p.hdr->aborted) != 0u;
 
-    if (warp < GD_CONSUMER_WARPS) {
+    if (warp < GD_CONSUMER_WARPS && !aborted) {
         const int ld4 = p.ld >> 2;
         const int n_groups = (ld4 + 31) / 32;                 // 32 float4 columns per group
         float4* sred = reinterpret_cast<float4*>(smem_raw);   // [8][32] float4, ring is idle now
@@ -132,11 +136,14 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
             // last CTA: every CTA is past the barrier wait -> safe to recycle the counters
             p.hdr->barrier = 0;
             p.hdr->done = 0;
-            for (int j = 0; j < p.n_jobs; ++j)
-                if (p.job_flag[j]) st_arrival_time(p.job_flag[j]);
-            __threadfence_system();
-            for (int j = 0; j < p.n_jobs; ++j)
-                if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);      // ordered by the fence above
+            p.hdr->aborted = 0;
+            if (!aborted) {
+                for (int j = 0; j < p.n_jobs; ++j)
+                    if (p.job_flag[j]) st_arrival_time(p.job_flag[j]);
+                __threadfence_system();
+                for (int j = 0; j < p.n_jobs; ++j)
+                    if (p.job_flag[j]) st_relaxed_sys(p.job_flag[j], p.stamp);      // ordered by the fence above
+            }
         }
     }
 }
@@ -169,6 +176,22 @@ __device__ __forceinline__ uint32_t wait_for_parameters(const Params& p) {
         code = v & 3u;
     }
     return code;
+}
+
+// Abandoning a round in flight (GradParams::abandon).  The producer lane looks at the parameter flag every
+// eighth tile; when the flag has passed this message's stamp the round was decided without it, so the lane
+// stops issuing loads at tile k: it waits until the ring slot of tile k is free, publishes `*s_stop = k`,
+// raises hdr->aborted and completes the slot's `full` barrier without data so that consumers already waiting
+// for tile k wake up.  Consumers test `*s_stop` before and after every wait and leave their tile loop at k.
+// All CTAs still meet in the device-wide barrier of reduce_and_ship, which then ships nothing.
+__device__ __forceinline__ bool round_is_over(const GradParams& p) {
+    return p.beta_flag != nullptr && ld_acquire_sys(p.beta_flag) > p.stamp;
+}
+__device__ __forceinline__ void producer_abandon(const GradParams& p, volatile long long* s_stop, long long k, uint64_t* full_k) {
+    *s_stop = k;
+    __threadfence_block();
+    atomicExch(&p.hdr->aborted, 1u);
+    mbar_arrive(full_k);
 }
 
 // host-side launchers (defined next to their kernels)

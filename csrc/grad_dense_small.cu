@@ -40,11 +40,14 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + (size_t)p.n_stages * stage_bytes);
     uint64_t* empty = full + GD_MAX_STAGES;
     __shared__ uint32_t s_decision;
+    __shared__ long long s_stop_store;
+    volatile long long* s_stop = &s_stop_store;
 
     const JobView jv = job_of_cta(p);
     const long long my_steps = (jv.bl < jv.n_steps) ? (jv.n_steps - jv.bl + jv.Gj - 1) / jv.Gj : 0;
 
     if (tid == 0) {
+        s_stop_store = NO_STOP;
         for (int s = 0; s < p.n_stages; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], GD_CONSUMER_WARPS);
@@ -88,6 +91,10 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
                 const int st = (int)(k % p.n_stages);
                 const uint32_t use = (uint32_t)(k / p.n_stages);
                 mbar_wait_backoff(&empty[st], (use - 1) & 1);
+                if (p.abandon && (k & 7) == 0 && round_is_over(p)) {
+                    producer_abandon(p, s_stop, k, &full[st]);
+                    break;
+                }
                 issue(k);
             }
         }
@@ -125,7 +132,9 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
             const int nr = (p.rows_per_seg - row0) < RB ? (p.rows_per_seg - row0) : RB;
             const float cf = p.coeff[sg];
             const float* ys = p.seg_y[sg] + row0;
+            if (p.abandon && k >= *s_stop) break;
             mbar_wait(&full[st], use & 1);
+            if (p.abandon && k >= *s_stop) break;
             const uint4* tile = reinterpret_cast<const uint4*>(stages + (size_t)st * stage_bytes);
             for (int r0 = 0; r0 < nr; r0 += rows_per_pass) {
                 float x[U][DVW][E];

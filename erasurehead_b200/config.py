@@ -109,6 +109,9 @@ class RunConfig:
     decoder: str = "concurrent"            # concurrent: the decoder runs on its own high-priority stream on SMs the
                                            # gradient kernels leave free (a round costs max(compute, wait));
                                            # inline: after the root's gradient kernels on one stream (compute + wait)
+    abandon: bool = False                  # dense single-column workers stop streaming X once the round they work for
+                                           # has been decided without them (true skipping of a straggler's compute;
+                                           # the reference can only cancel the send, coded.py:178-180, README.md:122)
     init: str = "scheme"                   # starting point: scheme (reference: randn for naive/replication/approx,
                                            # zeros otherwise -- SURVEY Q8) | zeros | randn
     debug_poison: bool = False             # fill every message slot with NaN before a run (stale-read detector)

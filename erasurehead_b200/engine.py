@@ -259,6 +259,7 @@ class Engine:
             self._setup_decoder()
         plan = _lib.RoundPlan()
         plan.n_jobs = self.n_jobs
+        plan.abandon = int(bool(cfg.abandon))
         plan.jobs = C.cast(self._jobs, C.POINTER(_lib.WorkerJob))
         plan.d_ws_local, plan.d_ws_root = self.ws.local, self.ws.root
         plan.d_scratch, plan.scratch_bytes = self.scratch.ptr(), self.scratch.nbytes

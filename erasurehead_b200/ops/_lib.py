@@ -44,7 +44,7 @@ class GradJob(C.Structure):
                 ("d_beta_flag", C.c_void_p), ("d_err", C.c_void_p),
                 ("n_segs", C.c_int32), ("rows_per_seg", C.c_int32), ("d", C.c_int32), ("ld", C.c_int32),
                 ("model", C.c_int32), ("stamp", C.c_uint32), ("timeout_ns", C.c_uint64),
-                ("x_bf16", C.c_int32), ("reserved", C.c_int32)]
+                ("x_bf16", C.c_int32), ("abandon", C.c_int32)]
 
 
 class GradEllJob(C.Structure):
@@ -93,7 +93,7 @@ class DecoderDesc(C.Structure):
 
 
 class RoundPlan(C.Structure):
-    _fields_ = [("n_jobs", C.c_int32), ("reserved", C.c_int32), ("jobs", C.POINTER(WorkerJob)),
+    _fields_ = [("n_jobs", C.c_int32), ("abandon", C.c_int32), ("jobs", C.POINTER(WorkerJob)),
                 ("d_ws_local", C.c_void_p), ("d_ws_root", C.c_void_p), ("d_scratch", C.c_void_p),
                 ("d_beta_local", C.c_void_p), ("scratch_bytes", C.c_size_t), ("decoder", C.POINTER(DecoderDesc)),
                 ("timeout_ns", C.c_uint64), ("lay", WsLayout),

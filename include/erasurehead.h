@@ -103,7 +103,10 @@ typedef struct eh_grad_job {
     uint32_t        stamp;          /* round + 1 */
     uint64_t        timeout_ns;     /* watchdog for the beta wait (0 = 30 s) */
     int32_t         x_bf16;         /* 0: d_X are fp32 rows; 1: bf16 rows (ld in elements, ld % 8 == 0) */
-    int32_t         reserved;
+    int32_t         abandon;        /* 1: while streaming, watch d_beta_flag; once it passes `stamp` (the round this
+                                       message belongs to has been decided without it) stop reading X and publish
+                                       nothing -- a straggler's compute is skipped, not just its message.  The
+                                       reference can only cancel the send (coded.py:178-180, README.md:122) */
 } eh_grad_job;
 
 size_t eh_grad_dense_scratch_bytes(int d);
@@ -291,7 +294,8 @@ typedef struct eh_worker_job {
 } eh_worker_job;
 
 typedef struct eh_round_plan {
-    int32_t  n_jobs, reserved;
+    int32_t  n_jobs;
+    int32_t  abandon;                /* dense single-column messages: see eh_grad_job.abandon */
     const eh_worker_job* jobs;       /* host array */
     void*    d_ws_local;             /* this GPU's workspace (parameters + parameter flag) */
     void*    d_ws_root;              /* the root's workspace as mapped here (slots + arrival flags) */

@@ -363,3 +363,28 @@ def test_engine_runs_on_device_generated_onehot_shapes(model, classes):
     assert np.all(np.isfinite(res.betaset))
     assert ev.training_loss[-1] < ev.training_loss[0]
     eng.close()
+
+
+def test_abandon_skips_the_compute_of_workers_whose_round_is_over():
+    """--abandon: a gradient kernel that is still streaming when the stop rule fires stops reading X and ships
+    nothing (the reference can only cancel the send, README.md:122).  Four 4 GiB messages back to back on one
+    GPU, n_collect = 2: workers 2 and 3 are abandoned every round, so a round costs about two messages
+    instead of four, with the same iterates."""
+    n, s, k, d, rpp, R = 4, 1, 2, 1024, 524288, 5
+    cfg = mk("approx", n=n, s=s, k=k, rows=n * rpp, d=d, rounds=R, synthetic=True, seed=1)
+    dl = np.tile(np.array([20e-6, 10e-6, 10e-6, 10e-6]), (R, 1))
+    plain = Engine(cfg, None, delays=dl)
+    r0 = plain.run()
+    plain.close()
+    eng = Engine(cfg.replace(abandon=True), None, delays=dl)
+    r1 = eng.run()
+    eng.close()
+    assert np.allclose(r1.betaset, r0.betaset, atol=1e-6)
+    assert np.array_equal(r1.worker_timeset >= 0, r0.worker_timeset >= 0)
+    job = r1.done[1, 1] - r1.done[1, 0]
+    # without abandoning, worker 2's kernel starts before the decoder has published the new round and runs to the
+    # end (worker 3's then skips at launch): ~3 messages of streaming per round
+    assert r0.timeset[1:].mean() > 2.6 * job
+    # with it, worker 2 stops within a few tiles: ~2 messages per round
+    assert r1.timeset[1:].mean() < 2.3 * job
+    assert np.all(r1.done[1:, 2:] < 0)           # their messages never arrived
