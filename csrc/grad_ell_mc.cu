@@ -37,7 +37,10 @@ struct EllMcHdr {
     alignas(128) uint32_t pad;
 };
 
+struct EllMcParams;
+__device__ __forceinline__ bool getenv_table_on(const EllMcParams& p);
 struct EllMcParams {
+    int hot_table;                   // 0 switches the per-CTA table off (EH_ELL_MC_TABLE=0, for A/B measurements)
     const int32_t* seg_idx[GEM_MAX_SEGS];
     const float* seg_y[GEM_MAX_SEGS];
     float coeff[GEM_MAX_SEGS];
@@ -55,24 +58,65 @@ struct EllMcParams {
     uint32_t* job_flag[GEM_MAX_JOBS];
 };
 
+__device__ __forceinline__ bool getenv_table_on(const EllMcParams& p) { return p.hot_table != 0; }
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// Per-CTA table for the popular levels.  A same-address L2 reduction costs ~10 ns, so the most popular level of a
+// categorical column (a fifth of all rows hit it) bounds the whole kernel when every hit goes to L2: 75 K hits
+// -> 0.79 ms at the Covertype x 7 shape.  Each CTA therefore keeps a direct-mapped table of GEM_TABLE features (two-way) in
+// shared memory: a feature claims a free slot with a CAS on first use, later hits are eight native integer
+// shared-memory adds of the fixed-point residuals (fp32 shared-memory atomics are CAS loops on sm_100), slot
+// collisions fall through to the L2 reduction, and the table is flushed with two L2 reductions per occupied slot
+// at the end.  Fixed point: |coeff * residual| <= cmax < 2^e2 is scaled to 30 - R2 bits for 2^R2 rows per CTA;
+// the table is used when that leaves at least 18 bits (<= 4096 rows per CTA), otherwise every hit goes to L2.
+constexpr int GEM_TABLE = 4096;
+constexpr int GEM_TABLE_BITS = 12;
+
 // run-length cache of one lane: the feature it is accumulating for and the residual vector so far
 struct LaneRun {
-    int col;
+    int col, n;          // feature and number of rows accumulated
     float v[GEM_CP];
 };
-__device__ __forceinline__ void run_flush(float* g, LaneRun& R) {
+struct HotTable {
+    int* tag;            // [GEM_TABLE], -1 = free
+    int* val;            // [GEM_TABLE][8] fixed point
+    float scale;         // 0 = table off
+};
+__device__ __forceinline__ void scatter(float* g, const HotTable& T, int col, const float (&v)[GEM_CP]) {
+    if (T.scale != 0.f) {
+        uint32_t slot = ((uint32_t)col * 2654435761u) >> (32 - GEM_TABLE_BITS);
+#pragma unroll
+        for (int probe = 0; probe < 2; ++probe, slot ^= 1u) {       // two-way: the slot and its neighbour
+            int t = T.tag[slot];
+            if (t == -1) {
+                const int old = atomicCAS(&T.tag[slot], -1, col);
+                t = (old == -1) ? col : old;
+            }
+            if (t == col) {
+#pragma unroll
+                for (int c = 0; c < GEM_CP; ++c) atomicAdd(&T.val[slot * GEM_CP + c], __float2int_rn(v[c] * T.scale));
+                return;
+            }
+        }
+    }
+    red_add_v4(g + (size_t)col * GEM_CP, v[0], v[1], v[2], v[3]);
+    red_add_v4(g + (size_t)col * GEM_CP + 4, v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void run_flush(float* g, const HotTable& T, LaneRun& R) {
     if (R.col >= 0) {
+        // a run longer than a few rows (the bias feature: every row) would overflow the fixed-point slot: straight to L2
         red_add_v4(g + (size_t)R.col * GEM_CP, R.v[0], R.v[1], R.v[2], R.v[3]);
         red_add_v4(g + (size_t)R.col * GEM_CP + 4, R.v[4], R.v[5], R.v[6], R.v[7]);
     }
 }
-__device__ __forceinline__ void run_add(float* g, LaneRun& R, int col, const float (&r)[GEM_CP]) {
+__device__ __forceinline__ void run_add(float* g, const HotTable& T, LaneRun& R, int col, const float (&r)[GEM_CP]) {
     if (col != R.col) {
-        run_flush(g, R);
+        if (R.col >= 0 && R.n == 1) scatter(g, T, R.col, R.v);        // a single hit: through the table
+        else run_flush(g, T, R);
+        R.n = 0;
         R.col = col;
 #pragma unroll
         for (int c = 0; c < GEM_CP; ++c) R.v[c] = r[c];
@@ -80,12 +124,18 @@ __device__ __forceinline__ void run_add(float* g, LaneRun& R, int col, const flo
 #pragma unroll
         for (int c = 0; c < GEM_CP; ++c) R.v[c] += r[c];
     }
+    R.n += 1;
 }
 
 __global__ void __launch_bounds__(GEM_THREADS) grad_ell_mc_kernel(const EllMcParams p) {
     __shared__ uint32_t s_code;
+    extern __shared__ __align__(16) int gem_smem[];               // tags, then values
+    int* s_tag = gem_smem;
+    int* s_val = gem_smem + GEM_TABLE;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int G = gridDim.x, b = blockIdx.x;
+    for (int i = tid; i < GEM_TABLE; i += GEM_THREADS) s_tag[i] = -1;
+    for (int i = tid; i < GEM_TABLE * GEM_CP; i += GEM_THREADS) s_val[i] = 0;
     int jb = 0;
     while (jb + 1 < p.n_jobs && b >= p.job_cta0[jb + 1]) ++jb;
     const int b0 = p.job_cta0[jb], Gj = p.job_cta0[jb + 1] - b0, bl = b - b0, seg0 = p.job_seg0[jb];
@@ -136,13 +186,46 @@ __global__ void __launch_bounds__(GEM_THREADS) grad_ell_mc_kernel(const EllMcPar
     const float4* W4 = reinterpret_cast<const float4*>(p.W);
     LaneRun run0, run1;
     run0.col = run1.col = -1;
+    run0.n = run1.n = 0;
+    // fixed-point format of the table (see HotTable): bound on |coeff * residual| and rows this CTA adds up
+    HotTable T;
+    T.tag = s_tag; T.val = s_val; T.scale = 0.f;
+    int e2 = 0, fbits = 0;
+    {
+        float cmax = 0.f;
+        for (int i = 0; i < p.job_nsegs[jb]; ++i) cmax = fmaxf(cmax, fabsf(p.coeff[seg0 + i]));
+        if (!(cmax > 1e-30f)) cmax = 1e-30f;
+        frexpf(cmax, &e2);                                         // softmax / logistic residuals are <= 1 in magnitude
+        const long long rows_cta = (long long)((job_rows + nwarps - 1) / nwarps) * (GEM_THREADS / 32);
+        int R2 = 0;
+        while ((1ll << R2) < rows_cta) ++R2;
+        fbits = 30 - R2;
+        if (fbits >= 18 && getenv_table_on(p)) T.scale = ldexpf(1.0f, fbits - e2);
+    }
     int sg = seg0 + gwarp / rps, lr = gwarp % rps;
+    // the next row's indices, label and weight are requested one iteration ahead (index stream latency)
+    const int32_t* ri_n = nullptr;
+    int c0_n = -1, c1_n = -1, sg_n = sg, lr_n = lr;
+    float y_n = 0.f;
+    auto fetch = [&](int row) {
+        if (row < job_rows) {
+            ri_n = p.seg_idx[sg_n] + (size_t)lr_n * nnz;
+            c0_n = l0 ? __ldg(ri_n + lane) : -1;
+            c1_n = l1 ? __ldg(ri_n + lane + 32) : -1;
+            y_n = __ldg(p.seg_y[sg_n] + lr_n);
+        }
+    };
+    fetch(gwarp);
     for (int row = gwarp; row < job_rows; row += nwarps) {
-        const int32_t* ri = p.seg_idx[sg] + (size_t)lr * nnz;
-        const int c0 = l0 ? __ldg(ri + lane) : -1;
-        const int c1 = l1 ? __ldg(ri + lane + 32) : -1;
-        const int yc = (int)__ldg(p.seg_y[sg] + lr);
+        const int32_t* ri = ri_n;
+        const int c0 = c0_n, c1 = c1_n;
+        const float yraw = y_n;
+        const int yc = (int)yraw;
+        sg = sg_n; lr = lr_n;
         const float cf = p.coeff[sg];
+        lr_n += nwarps;
+        while (lr_n >= rps) { lr_n -= rps; ++sg_n; }
+        fetch(row + nwarps);
         float lg[GEM_CP];
 #pragma unroll
         for (int c = 0; c < GEM_CP; ++c) lg[c] = 0.f;
@@ -188,24 +271,36 @@ __global__ void __launch_bounds__(GEM_THREADS) grad_ell_mc_kernel(const EllMcPar
             se += __shfl_xor_sync(0xffffffffu, se, 16);
             r = cf * (__fdividef(e, se) - (cls == yc ? 1.f : 0.f));
         } else {                                               // C independent logistic columns, labels +-1 (model 3)
-            const float yv = __ldg(p.seg_y[sg] + lr);
+            const float yv = yraw;
             r = cls < p.C ? cf * __fdividef(-yv, __expf(m * yv) + 1.0f) : 0.f;
         }
         float rv[GEM_CP];
 #pragma unroll
         for (int c = 0; c < GEM_CP; ++c) rv[c] = __shfl_sync(0xffffffffu, r, 4 * c);
-        if (c0 >= 0) run_add(gacc, run0, c0, rv);
-        if (c1 >= 0) run_add(gacc, run1, c1, rv);
+        if (c0 >= 0) run_add(gacc, T, run0, c0, rv);
+        if (c1 >= 0) run_add(gacc, T, run1, c1, rv);
         for (int k = lane + 64; k < nnz; k += 32) {
             const int c = __ldg(ri + k);
             red_add_v4(gacc + (size_t)c * GEM_CP, rv[0], rv[1], rv[2], rv[3]);
             red_add_v4(gacc + (size_t)c * GEM_CP + 4, rv[4], rv[5], rv[6], rv[7]);
         }
-        lr += nwarps;
-        while (lr >= rps) { lr -= rps; ++sg; }
     }
-    run_flush(gacc, run0);
-    run_flush(gacc, run1);
+    run_flush(gacc, T, run0);
+    run_flush(gacc, T, run1);
+    __syncthreads();
+    if (T.scale != 0.f) {
+        const float inv = ldexpf(1.0f, e2 - fbits);
+        for (int i = tid; i < GEM_TABLE; i += GEM_THREADS) {
+            const int t = s_tag[i];
+            if (t >= 0) {
+                float v[GEM_CP];
+#pragma unroll
+                for (int c = 0; c < GEM_CP; ++c) v[c] = (float)s_val[i * GEM_CP + c] * inv;
+                red_add_v4(gacc + (size_t)t * GEM_CP, v[0], v[1], v[2], v[3]);
+                red_add_v4(gacc + (size_t)t * GEM_CP + 4, v[4], v[5], v[6], v[7]);
+            }
+        }
+    }
 
     grid_barrier(&p.hdr->barrier, gen);               // all reductions have landed
 
@@ -275,6 +370,7 @@ extern "C" int eh_grad_ell_mc_multi(const eh_grad_ell_job* jobs, int n_jobs, int
         }
     }
     p.n_jobs = n_jobs;
+    p.hot_table = (getenv("EH_ELL_MC_TABLE") && atoi(getenv("EH_ELL_MC_TABLE")) == 0) ? 0 : 1;
     p.W = j->d_beta; p.beta_flag = j->d_beta_flag; p.err = j->d_err;
     p.hdr = reinterpret_cast<EllMcHdr*>(d_scratch);
     p.gacc = reinterpret_cast<float*>(reinterpret_cast<char*>(d_scratch) + sizeof(EllMcHdr));
@@ -282,8 +378,10 @@ extern "C" int eh_grad_ell_mc_multi(const eh_grad_ell_job* jobs, int n_jobs, int
     p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     // CTAs per message in proportion to its partitions; at least one warp-row of work per warp
+    const size_t smem = (size_t)GEM_TABLE * (1 + GEM_CP) * sizeof(int);
+    EH_SET_MAX_SMEM(grad_ell_mc_kernel, smem);
     int occ = 0;
-    EH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, grad_ell_mc_kernel, GEM_THREADS, 0));
+    EH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, grad_ell_mc_kernel, GEM_THREADS, smem));
     if (occ > 2) occ = 2;
     if (occ < 1) occ = 1;
     const long long total_rows = (long long)j->rows_per_seg * nseg;
@@ -301,6 +399,6 @@ extern "C" int eh_grad_ell_mc_multi(const eh_grad_ell_job* jobs, int n_jobs, int
         p.job_cta0[q + 1] = used;
     }
     void* args[] = {(void*)&p};
-    return launch_grid_sync((const void*)grad_ell_mc_kernel, dim3((unsigned)used), dim3(GEM_THREADS), args, 0,
+    return launch_grid_sync((const void*)grad_ell_mc_kernel, dim3((unsigned)used), dim3(GEM_THREADS), args, smem,
                             (cudaStream_t)stream);
 }
