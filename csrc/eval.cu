@@ -172,7 +172,141 @@ static AucLayout auc_layout(long long n) {
     return L;
 }
 
+// ---------------------------------------------------------------- ROC-AUC of R score columns in one pass
+// One device-wide radix sort of 64-bit keys (column id << 32 | descending-order bits of the score) replaces R
+// separate sorts; the positive counts and tie-group starts are two scans over the whole array, and every column
+// subtracts the running total at its own start.  Same tie-aware trapezoid as above (sklearn roc_curve + auc,
+// naive.py:196-197), one launch sequence for all iterates of the evaluation epilogue.
+__device__ __forceinline__ uint32_t desc_bits(float f) {
+    if (f == 0.f) f = 0.f;                                   // -0 and +0 tie
+    uint32_t u = __float_as_uint(f);
+    u ^= (u >> 31) ? 0xffffffffu : 0x80000000u;              // ascending order-preserving
+    return ~u;                                               // descending
+}
+__global__ void aucb_keys_kernel(const float* __restrict__ S, const float* __restrict__ lab, long long n, int R,
+                                 unsigned long long* __restrict__ keys, unsigned char* __restrict__ vals) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * R) return;
+    const long long seg = i / n, j = i - seg * n;
+    keys[i] = ((unsigned long long)seg << 32) | desc_bits(S[i]);
+    vals[i] = lab[j] > 0.f ? 1 : 0;
+}
+__global__ void aucb_prepare_kernel(const unsigned long long* __restrict__ keys, const unsigned char* __restrict__ vals,
+                                    long long n, long long total, int* __restrict__ is_pos, long long* __restrict__ gstart) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    is_pos[i] = vals[i];
+    gstart[i] = (i == 0 || keys[i - 1] != keys[i]) ? i : 0;   // a new column is a new key: also a group start
+}
+__global__ void __launch_bounds__(256) aucb_area_kernel(const unsigned long long* __restrict__ keys,
+                                                        const long long* __restrict__ cumpos,
+                                                        const long long* __restrict__ gstart, long long n,
+                                                        double* __restrict__ area) {
+    const long long seg = blockIdx.y, base = seg * n;
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double a = 0.0;
+    if (j < n) {
+        const long long i = base + j;
+        if (j == n - 1 || keys[i] != keys[i + 1]) {          // i closes a tie group = one ROC vertex
+            const long long cb = base > 0 ? cumpos[base - 1] : 0;
+            const long long gs = gstart[i];
+            const long long tp_prev = gs > base ? cumpos[gs - 1] - cb : 0;
+            const long long fp_prev = (gs - base) - tp_prev;
+            const long long tp = cumpos[i] - cb;
+            const long long fp = (j + 1) - tp;
+            a = (double)(fp - fp_prev) * 0.5 * (double)(tp + tp_prev);
+        }
+    }
+    a = warp_sum(a);
+    __shared__ double sh[8];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        if (t != 0.0) atomicAdd(area + seg, t);
+    }
+}
+__global__ void aucb_finish_kernel(const long long* __restrict__ cumpos, long long n, int R, const double* __restrict__ area,
+                                   double* __restrict__ out) {
+    const int seg = blockIdx.x * blockDim.x + threadIdx.x;
+    if (seg >= R) return;
+    const long long base = (long long)seg * n;
+    const double Pn = (double)(cumpos[base + n - 1] - (base > 0 ? cumpos[base - 1] : 0));
+    const double Nn = (double)n - Pn;
+    out[seg] = (Pn > 0.0 && Nn > 0.0) ? area[seg] / (Pn * Nn) : nan("");
+}
+
+struct AucBatchLayout {
+    size_t off_k0, off_k1, off_v0, off_v1, off_pos, off_cum, off_gs, off_area, off_tmp, tmp_bytes, total;
+};
+static AucBatchLayout aucb_layout(long long n, int R) {
+    AucBatchLayout L;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t T = (size_t)n * R;
+    size_t off = 0;
+    L.off_k0 = off; off += up(T * 8);
+    L.off_k1 = off; off += up(T * 8);
+    L.off_v0 = off; off += up(T);
+    L.off_v1 = off; off += up(T);
+    L.off_pos = off; off += up(T * sizeof(int));
+    L.off_cum = off; off += up(T * sizeof(long long));
+    L.off_gs = off;  off += up(T * sizeof(long long));
+    L.off_area = off; off += up((size_t)R * sizeof(double));
+    size_t t1 = 0, t2 = 0, t3 = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, t1, (const unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                    (const unsigned char*)nullptr, (unsigned char*)nullptr, (long long)T);
+    cub::DeviceScan::InclusiveSum(nullptr, t2, (const int*)nullptr, (long long*)nullptr, (long long)T);
+    cub::DeviceScan::InclusiveScan(nullptr, t3, (const long long*)nullptr, (long long*)nullptr, cub::Max(), (long long)T);
+    L.tmp_bytes = t1 > t2 ? t1 : t2;
+    if (t3 > L.tmp_bytes) L.tmp_bytes = t3;
+    L.off_tmp = off;
+    off += up(L.tmp_bytes);
+    L.total = off;
+    return L;
+}
+
 }  // namespace eh
+
+extern "C" size_t eh_auc_batch_scratch_bytes(int64_t n, int R) { return (n > 0 && R > 0) ? eh::aucb_layout(n, R).total : 0; }
+
+extern "C" int eh_auc_batch(const float* d_scores, const float* d_labels, int64_t n, int R, double* d_auc, void* d_scratch,
+                            size_t scratch_bytes, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(d_scores && d_labels && d_auc && d_scratch && n > 0 && R > 0, "auc_batch: bad argument");
+    EH_REQUIRE(n < (1ll << 31) && (long long)n * R < (1ll << 40), "auc_batch: too many scores");
+    const AucBatchLayout L = aucb_layout(n, R);
+    EH_REQUIRE(scratch_bytes >= L.total, "auc_batch: scratch too small (%zu < %zu)", scratch_bytes, L.total);
+    char* base = (char*)d_scratch;
+    unsigned long long* k0 = (unsigned long long*)(base + L.off_k0);
+    unsigned long long* k1 = (unsigned long long*)(base + L.off_k1);
+    unsigned char* v0 = (unsigned char*)(base + L.off_v0);
+    unsigned char* v1 = (unsigned char*)(base + L.off_v1);
+    int* pos = (int*)(base + L.off_pos);
+    long long* cum = (long long*)(base + L.off_cum);
+    long long* gs = (long long*)(base + L.off_gs);
+    double* area = (double*)(base + L.off_area);
+    void* tmp = base + L.off_tmp;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long T = (long long)n * R;
+    const unsigned gridT = (unsigned)((T + 255) / 256);
+    aucb_keys_kernel<<<gridT, 256, 0, st>>>(d_scores, d_labels, n, R, k0, v0);
+    int seg_bits = 1;
+    while ((1ll << seg_bits) < R) ++seg_bits;
+    size_t tb = L.tmp_bytes;
+    EH_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, v0, v1, T, 0, 32 + seg_bits, st));
+    aucb_prepare_kernel<<<gridT, 256, 0, st>>>(k1, v1, n, T, pos, gs);
+    tb = L.tmp_bytes;
+    EH_CUDA(cub::DeviceScan::InclusiveSum(tmp, tb, pos, cum, T, st));
+    tb = L.tmp_bytes;
+    EH_CUDA(cub::DeviceScan::InclusiveScan(tmp, tb, gs, gs, cub::Max(), T, st));
+    EH_CUDA(cudaMemsetAsync(area, 0, (size_t)R * sizeof(double), st));
+    dim3 grid((unsigned)((n + 255) / 256), (unsigned)R);
+    aucb_area_kernel<<<grid, 256, 0, st>>>(k1, cum, gs, n, area);
+    aucb_finish_kernel<<<(R + 127) / 128, 128, 0, st>>>(cum, n, R, area, d_auc);
+    EH_CUDA(cudaGetLastError());
+    return EH_OK;
+}
 
 extern "C" int eh_margins_dense(const float* d_X, int64_t rows, int d, int ld, const float* d_Bt, int R, int ldb,
                                 float* d_P, void* stream) {

@@ -609,26 +609,28 @@ class Engine:
         Xt, yt = self._device_test()
         if self.sparse:
             return self._evaluate_gpu_mc_ell(betaset, n_parts, Xt, yt)
-        tr, te = np.zeros(R), np.zeros(R)
-        for i in range(R):
-            Wp = torch.from_numpy(pack_mc(betaset[i]).astype(np.float32)).to(dev)
-            tot, rows = 0.0, 0
-            for p in range(n_parts):
-                Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
-                if Xp.dtype != torch.float32:
-                    Xp = Xp.float()                  # the loss-only kernels read fp32 rows
-                tot += float(mc.loss_mc(Xp, yp, Wp, d, C_, self.model.device_id).item())
-                rows += Xp.shape[0]
-            tr[i] = tot / rows
-            te[i] = float(mc.loss_mc(Xt, yt, Wp, d, C_, self.model.device_id).item()) / Xt.shape[0]
-        # test accuracy: margins of all classes through the tensor-core evaluation kernel, argmax per row
+        # sums stay on the device; one host read per quantity at the end
+        tr = torch.zeros(R, dtype=torch.float64, device=dev)
+        te = torch.zeros(R, dtype=torch.float64, device=dev)
+        acc = torch.zeros(R, dtype=torch.float64, device=dev)
         from .ops import metrics as mops
-        acc = np.zeros(R)
+        Wall = torch.from_numpy(pack_mc(betaset).astype(np.float32)).to(dev)            # [R, CN * ldw]
+        WT = torch.zeros((R, C_, _pad32(d)), dtype=torch.float32, device=dev)           # class-major rows for eval_tc
+        WT[:, :, :d] = torch.from_numpy(np.ascontiguousarray(np.swapaxes(betaset, 1, 2))).to(dev)
+        rows = 0
+        parts = []
+        for p in range(n_parts):
+            Xp, yp = self.parts[p] if p in self.parts else self._device_partition(p)
+            parts.append((Xp.float() if Xp.dtype != torch.float32 else Xp, yp))      # the loss-only kernels read fp32 rows
+            rows += Xp.shape[0]
         for i in range(R):
-            Wi = torch.zeros((C_, _pad32(d)), dtype=torch.float32, device=dev)
-            Wi[:, :d] = torch.from_numpy(np.ascontiguousarray(betaset[i].T)).to(dev)
-            _, M = mops.eval_tc(Xt, Wi, None, d=d, want_margins=True)
-            acc[i] = float((M[:, :C_].argmax(dim=1) == yt.long()).float().mean().item())
+            for Xp, yp in parts:
+                tr[i] += mc.loss_mc(Xp, yp, Wall[i], d, C_, self.model.device_id)
+            te[i] = mc.loss_mc(Xt, yt, Wall[i], d, C_, self.model.device_id)
+            # test accuracy: margins of all classes through the tensor-core evaluation kernel, argmax per row
+            _, M = mops.eval_tc(Xt, WT[i], None, d=d, want_margins=True)
+            acc[i] = (M[:, :C_].argmax(dim=1) == yt.long()).double().mean()
+        tr, te, acc = (tr / rows).cpu().numpy(), (te / Xt.shape[0]).cpu().numpy(), acc.cpu().numpy()
         return results.Evaluation(tr, te, None, acc)
 
     def _evaluate_gpu_mc_ell(self, betaset: np.ndarray, n_parts: int, Xt, yt):
@@ -709,7 +711,7 @@ class Engine:
         auc = None
         if self.model.has_auc:
             Pcol = Pt.t().contiguous()
-            auc = torch.stack([mops.auc(Pcol[i], yt) for i in range(R)]).cpu().numpy()
+            auc = mops.auc_batch(Pcol[:R], yt).cpu().numpy()            # all iterates: one sort, two scans
         acc = None
         if self.model.name != "linear":
             pred = torch.where(Pt[:, :R] > 0, 1.0, -1.0)

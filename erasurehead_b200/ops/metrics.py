@@ -48,6 +48,23 @@ def auc(scores: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def auc_batch(scores: torch.Tensor, labels: torch.Tensor, max_elems: int = 1 << 27) -> torch.Tensor:
+    """Tie-aware ROC-AUC of every row of ``scores[R, n]`` (one row per stored iterate) -> float64 ``[R]``.
+    One sort + two scans for all rows (``eh_auc_batch``); very large inputs go in chunks of rows."""
+    scores = scores.contiguous().float()
+    labels = labels.contiguous().float()
+    R, n = scores.shape
+    out = torch.empty(R, dtype=torch.float64, device=scores.device)
+    per = max(1, min(R, max_elems // max(1, n)))
+    nbytes = lib().eh_auc_batch_scratch_bytes(n, per)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=scores.device)
+    for r0 in range(0, R, per):
+        k = min(per, R - r0)
+        check(lib().eh_auc_batch(scores[r0:r0 + k].data_ptr(), labels.data_ptr(), n, k, out[r0:r0 + k].data_ptr(),
+                                 scratch.data_ptr(), nbytes, stream_ptr()), "eh_auc_batch")
+    return out
+
+
 def eval_tc(X: torch.Tensor, Bt: torch.Tensor, y: torch.Tensor | None = None, kind: int = 0, d: int | None = None,
             want_margins: bool = False, loss_sums: torch.Tensor | None = None):
     """tcgen05/TMEM evaluation: one pass over ``X`` for all ``R`` iterates (TF32 operands).

@@ -348,6 +348,11 @@ int eh_loss_columns(const float* d_P, const float* d_y, int64_t rows, int R, int
 int eh_auc(const float* d_scores, const float* d_labels, int64_t n, double* d_auc, void* d_scratch,
            size_t scratch_bytes, void* stream);
 size_t eh_auc_scratch_bytes(int64_t n);
+/* The same for R score columns at once (d_scores is [R][n], one column per stored iterate): ONE device-wide
+ * sort of (column, score) keys and two scans instead of R sort + scan sequences; d_auc receives R values. */
+int eh_auc_batch(const float* d_scores, const float* d_labels, int64_t n, int R, double* d_auc, void* d_scratch,
+                 size_t scratch_bytes, void* stream);
+size_t eh_auc_batch_scratch_bytes(int64_t n, int R);
 
 /* ------------------------------------------------------------------------------------------
  * Data / code generation on the device.

@@ -482,3 +482,21 @@ def test_synth_onehot_and_multiclass_labels_on_device():
     assert cd.numel() == 5 and cd.min().item() > 4096 // 50
     X0, _ = synth.synth_gmm(4096, 512, seed=5, partition=1, task=0)
     assert torch.equal(Xd, X0)              # the features do not depend on the label task
+
+
+def test_auc_batch_equals_per_column_auc():
+    """All iterates' ROC-AUC from one sort + two scans: identical to the per-column routine, ties included."""
+    from erasurehead_b200.ops import metrics as mops
+    torch.manual_seed(3)
+    n, R = 20011, 13
+    S = torch.randn(R, n, device=DEV)
+    S[2] = torch.round(S[2] * 2) / 2          # heavy ties
+    S[5] = 0.0                                # all tied -> 0.5
+    S[7, ::3] = -0.0
+    S[7, 1::3] = 0.0
+    y = torch.where(torch.rand(n, device=DEV) > 0.3, 1.0, -1.0)
+    got = mops.auc_batch(S, y)
+    want = torch.stack([mops.auc(S[i], y) for i in range(R)])
+    assert torch.allclose(got, want, rtol=0, atol=1e-12)
+    assert abs(got[5].item() - 0.5) < 1e-12
+    assert torch.allclose(mops.auc_batch(S, y, max_elems=3 * n), want, rtol=0, atol=1e-12)      # chunked path
