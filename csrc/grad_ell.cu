@@ -344,8 +344,9 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_smem_kernel(const Ell
 // requests the next four rows of a warp before it processes the current four.
 // No reference counterpart (scipy CSR^T matvec in float64, approximate_coding.py:194-196).
 // ---------------------------------------------------------------------------------------------
+constexpr int GFX_THREADS = 1024;            // fixed-point variant: 32 warps per SM hide the gather / shuffle / atomic chain
 template <bool BETA_IN_SMEM, bool WIDE>
-__global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllParams p, float* __restrict__ partials) {
+__global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllParams p, float* __restrict__ partials) {
     extern __shared__ __align__(16) float ges_smem[];
     // hi[d + 1], lo[d + 1] accumulator words (separate arrays: consecutive columns fall into consecutive banks),
     // then [d + 1] parameters; slot d is a dummy column that absorbs the padding lanes (a row of 55 ones
@@ -355,11 +356,11 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllPa
     int* acc_lo = acc_hi + dd;
     float* bsm = ges_smem + 2 * dd;
     __shared__ uint32_t s_code;
-    __shared__ float s_red[2][GES_THREADS / 32];
+    __shared__ float s_red[2][GFX_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int G = gridDim.x, b = blockIdx.x;
 
-    for (int c = tid; c <= p.d; c += GES_THREADS) { acc_hi[c] = 0; acc_lo[c] = 0; }
+    for (int c = tid; c <= p.d; c += GFX_THREADS) { acc_hi[c] = 0; acc_lo[c] = 0; }
 
     // which batched message this CTA works for
     int jb = 0;
@@ -369,8 +370,8 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllPa
     // instructions than the rest of the row's work
     const int rps = p.rows_per_seg;
     const int job_rows = rps * p.job_nsegs[jb];
-    const int gwarp = bl * (GES_THREADS / 32) + warp;
-    const int nwarps = Gj * (GES_THREADS / 32);
+    const int gwarp = bl * (GFX_THREADS / 32) + warp;
+    const int nwarps = Gj * (GFX_THREADS / 32);
     constexpr int RW = 4;                      // rows per warp and step
     const int nnz = p.nnz, dummy = p.d;
 
@@ -418,14 +419,14 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllPa
     // parameters -> shared memory (if they fit); |beta|max is needed only for the linear residual's bound
     float bmax = 0.f;
     if (BETA_IN_SMEM) {
-        for (int c = tid; c < p.d; c += GES_THREADS) {
+        for (int c = tid; c < p.d; c += GFX_THREADS) {
             const float t = __ldcg(p.beta + c);
             bsm[c] = t;
             bmax = fmaxf(bmax, fabsf(t));
         }
         if (tid == 0) bsm[dummy] = 0.f;
     } else if (p.model != EH_MODEL_LOGISTIC) {
-        for (int c = tid; c < p.d; c += GES_THREADS) bmax = fmaxf(bmax, fabsf(__ldcg(p.beta + c)));
+        for (int c = tid; c < p.d; c += GFX_THREADS) bmax = fmaxf(bmax, fabsf(__ldcg(p.beta + c)));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -436,13 +437,13 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllPa
     __syncthreads();
     ymax = 0.f; bmax = 0.f;
 #pragma unroll
-    for (int w = 0; w < GES_THREADS / 32; ++w) { ymax = fmaxf(ymax, s_red[0][w]); bmax = fmaxf(bmax, s_red[1][w]); }
+    for (int w = 0; w < GFX_THREADS / 32; ++w) { ymax = fmaxf(ymax, s_red[0][w]); bmax = fmaxf(bmax, s_red[1][w]); }
     // bound on |rs| and the fixed-point format
     float bound = (p.model == EH_MODEL_LOGISTIC) ? cmax * ymax : 2.0f * cmax * (ymax + (float)nnz * bmax);
     if (!(bound > 1e-30f)) bound = 1e-30f;
     int e2;
     frexpf(bound, &e2);                                            // bound < 2^e2
-    const long long rows_cta = (long long)((job_rows + nwarps * RW - 1) / (nwarps * RW)) * (GES_THREADS / 32) * RW;
+    const long long rows_cta = (long long)((job_rows + nwarps * RW - 1) / (nwarps * RW)) * (GFX_THREADS / 32) * RW;
     int R2 = 0;
     while ((1ll << R2) < rows_cta) ++R2;
     const int LB = R2 <= 16 ? 16 : 32 - R2;
@@ -545,7 +546,7 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllPa
     float* mine = partials + (size_t)b * p.d;
     const double inv = (double)ldexpf(1.0f, e2 - W);
     const double hi_w = (double)(1u << LB);
-    for (int c = tid; c < p.d; c += GES_THREADS) {
+    for (int c = tid; c < p.d; c += GFX_THREADS) {
         __stcg(mine + c, (float)(((double)acc_hi[c] * hi_w + (double)(unsigned)acc_lo[c]) * inv));
     }
 
@@ -556,7 +557,7 @@ __global__ void __launch_bounds__(GES_THREADS, 1) grad_ell_fx_kernel(const EllPa
     const int chunk = (p.d + Gj - 1) / Gj;
     const int c0 = bl * chunk, c1 = min(p.d, c0 + chunk);
     float* out = p.job_out[jb];
-    for (int c = c0 + tid; c < c1; c += GES_THREADS) {
+    for (int c = c0 + tid; c < c1; c += GFX_THREADS) {
         float t = 0.f;
         for (int g = b0; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
         out[c] = t;
@@ -648,7 +649,8 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
         // CTAs per message in proportion to its rows (32 rows of work per warp at least), every message >= 1
         const long long total_rows = (long long)j->rows_per_seg * nseg;
         long long grid = worker_sms();
-        const long long want = (total_rows * 32 + GES_THREADS - 1) / GES_THREADS;
+        const int threads = fx_variant ? GFX_THREADS : GES_THREADS;
+        const long long want = (total_rows * 32 + threads - 1) / threads;
         if (grid > want) grid = want;
         if (grid < n_jobs) grid = n_jobs;
         const long long spare = grid - n_jobs;
@@ -675,7 +677,7 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
             else { EH_SET_MAX_SMEM((grad_ell_smem_kernel<false>), (int)GES_SMEM_LIMIT); }
         }
         void* args[] = {(void*)&p, (void*)&partials};
-        return launch_grid_sync(kern, dim3((unsigned)grid), dim3(GES_THREADS), args, smem, (cudaStream_t)stream);
+        return launch_grid_sync(kern, dim3((unsigned)grid), dim3(threads), args, smem, (cudaStream_t)stream);
     }
     int occ = 0;
     EH_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, grad_ell_kernel, GE_THREADS, 0));
