@@ -59,6 +59,7 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
     __shared__ double s_wt[EH_MAX_WORKERS * EH_MAX_MSGS];
     __shared__ const float* s_src[EH_MAX_WORKERS * EH_MAX_MSGS];
     __shared__ int s_nsrc;
+    __shared__ int s_cnt[2 * EH_MAX_WORKERS / 32];
     __shared__ uint32_t s_go;
 
     DecScratch* sc = reinterpret_cast<DecScratch*>(D.d_scratch);
@@ -237,19 +238,35 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
 
     // ------------------------------------------------------------------ phase 2: decode + update + push
     if (!aborted) {
-        if (tid == 0) {
-            int c = 0;
-            for (int w = 0; w < n; ++w) {
-                const double a = __ldcg(&sc->a_coded[w]);
-                if (a != 0.0) { s_src[c] = ws_slot(ws0, D.lay, w, EH_MSG_CODED, parity); s_wt[c] = a; ++c; }
+        // source list (coded messages in worker order, then private ones): 128 threads fetch one weight each and
+        // compact with ballots -- a serial loop of n dependent L2 loads by one thread cost ~0.4 us per worker
+        {
+            const int e = tid;                                   // entry: 0..63 coded, 64..127 private
+            double a = 0.0;
+            if (e < EH_MAX_WORKERS) {
+                if (e < n) a = __ldcg(&sc->a_coded[e]);
+            } else if (e < 2 * EH_MAX_WORKERS && D.n_msgs > 1) {
+                if (e - EH_MAX_WORKERS < n) a = __ldcg(&sc->a_priv[e - EH_MAX_WORKERS]);
             }
-            if (D.n_msgs > 1) {
-                for (int w = 0; w < n; ++w) {
-                    const double a = __ldcg(&sc->a_priv[w]);
-                    if (a != 0.0) { s_src[c] = ws_slot(ws0, D.lay, w, EH_MSG_PRIVATE, parity); s_wt[c] = a; ++c; }
+            const bool nz = (tid < 2 * EH_MAX_WORKERS) && a != 0.0;
+            const unsigned m = __ballot_sync(0xffffffffu, nz);
+            if (tid < 2 * EH_MAX_WORKERS && lane == 0) s_cnt[warp] = __popc(m);
+            __syncthreads();
+            if (tid < 2 * EH_MAX_WORKERS) {
+                int base = 0;
+                for (int q = 0; q < warp; ++q) base += s_cnt[q];
+                if (nz) {
+                    const int c = base + __popc(m & ((1u << lane) - 1u));
+                    const bool priv = e >= EH_MAX_WORKERS;
+                    s_src[c] = ws_slot(ws0, D.lay, priv ? e - EH_MAX_WORKERS : e, priv ? EH_MSG_PRIVATE : EH_MSG_CODED, parity);
+                    s_wt[c] = a;
+                }
+                if (tid == 0) {
+                    int tot = 0;
+                    for (int q = 0; q < 2 * EH_MAX_WORKERS / 32; ++q) tot += s_cnt[q];
+                    s_nsrc = tot;
                 }
             }
-            s_nsrc = c;
         }
         __syncthreads();
         const int nsrc = s_nsrc;
