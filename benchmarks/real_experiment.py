@@ -38,7 +38,7 @@ SCHEMES = ["naive", "avoidstragg", "replication", "coded", "approx", "partial_re
 ETA = {"covtype": 0.3, "amazon-dataset": 1.0, "kc_house_data": 0.1}      # main.py:37-46 (schedules are edited per dataset there)
 
 
-def run_one(ctx, dataset, scheme, delay, rounds, model=None, classes=1):
+def run_one(ctx, dataset, scheme, delay, rounds, model=None, classes=1, impl="ours"):
     sh = DATASET_SHAPES[dataset]
     ic, pp, cv = triple_from_scheme(scheme, P if scheme.startswith("partial") else 0)
     s = 0 if scheme == "naive" else S
@@ -52,6 +52,20 @@ def run_one(ctx, dataset, scheme, delay, rounds, model=None, classes=1):
     cfg = RunConfig(N_WORKERS + 1, sh["n_rows"], sh["n_cols"], "", 1, dataset, ic, s, pp, cv, K, add_delay, "AGD",
                     rounds=rounds, synthetic=True, seed=1, delay_scale=scale, quiet=True, init="zeros",
                     eta0=ETA[dataset], model=model, classes=classes, **kw)
+    if impl == "nccl":
+        # baseline B2: NCCL broadcast / gather + cuSPARSE matvecs + torch decode, same data, delays and start
+        from erasurehead_b200.parallel.nccl_baseline import NcclBaselineEngine
+        b = NcclBaselineEngine(cfg, None, ctx=ctx)
+        _, ts = b.run(rounds)
+        b.close()
+        del b
+        gc.collect()
+        torch.cuda.empty_cache()
+        if not ctx.is_root:
+            return None
+        return {"impl": "nccl", "dataset": dataset, "scheme": scheme, "gpus": ctx.world, "n_workers": N_WORKERS, "s": s,
+                "delay": {"none": "none", "scaled": "exp(5 ms)", "stock": "exp(0.5 s)"}[delay], "rounds": rounds,
+                "mean_round_ms": float(ts[3:].mean() * 1e3), "median_round_ms": float(np.median(ts[3:]) * 1e3)}
     eng = Engine(cfg, None, ctx=ctx)
     res = eng.run()
     ev = eng.evaluate(res)
@@ -81,9 +95,23 @@ def main():
     ap.add_argument("--stock-rounds", type=int, default=6)
     ap.add_argument("--multiclass", action="store_true", help="also run Covertype-shaped 7-class softmax (replication, coded)")
     ap.add_argument("--out", default="")
+    ap.add_argument("--impl", default="ours", choices=["ours", "nccl"], help="nccl: baseline B2 round times only")
     a = ap.parse_args()
     ctx = init_distributed()
     out = []
+    if a.impl == "nccl":
+        for dataset in a.datasets.split(","):
+            for delay in a.delays.split(","):
+                for scheme in a.schemes.split(","):
+                    rec = run_one(ctx, dataset, scheme, delay, a.stock_rounds if delay == "stock" else a.rounds, impl="nccl")
+                    if rec:
+                        print(json.dumps(rec), flush=True)
+                        out.append(rec)
+        if a.out and ctx.is_root:
+            json.dump(out, open(a.out, "w"), indent=1)
+        if ctx.world > 1:
+            torch.distributed.destroy_process_group()
+        return
     for dataset in a.datasets.split(","):
         for delay in a.delays.split(","):
             R = a.stock_rounds if delay == "stock" else a.rounds

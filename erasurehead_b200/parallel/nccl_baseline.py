@@ -1,7 +1,8 @@
 """Baseline B2: the same schemes with library calls only.
 
 Per round, host-driven: NCCL broadcast of the parameters, each rank computes its workers'
-encoded gradients with two cuBLAS GEMVs + elementwise kernels (X is read twice), NCCL gather of
+encoded gradients with two cuBLAS GEMVs (dense data) or two cuSPARSE CSR matvecs (one-hot data)
++ elementwise kernels (X is read twice), NCCL gather of
 the messages to rank 0, which waits out the injected delay of the last message it needs (a
 device spin, same delay table as the product), decodes with torch ops and applies the update.
 This is what "a solution that only calls NCCL" looks like; it is measured by
@@ -59,15 +60,30 @@ class NcclBaselineEngine:
         self._clock_ghz = 1.9
         self._pin_out = None
 
+    def _csr(self, idx):
+        """One-hot ELL indices -> torch sparse CSR (and its transpose), the library format (cuSPARSE)."""
+        rows, nnz = idx.shape
+        crow = torch.arange(0, rows * nnz + 1, nnz, device=self.dev, dtype=torch.int64)
+        X = torch.sparse_csr_tensor(crow, idx.reshape(-1).long(), torch.ones(rows * nnz, device=self.dev),
+                                    size=(rows, self.cfg.n_cols))
+        return X, X.t().to_sparse_csr()
+
     def _partition(self, p):
         cfg = self.cfg
+        task = 1 if self.model.name == "linear" else 0
         if self.data is None:
             from ..ops import synth
-            X, y = synth.synth_gmm(self.spec.rows_per_part, cfg.n_cols, cfg.seed or 0, p, 0, self.dev)
+            if cfg.is_real:                     # --synthetic one-hot shape: same generator and seed as the product
+                from ..data.shapes import DATASET_SHAPES
+                nnz = cfg.synthetic_nnz or DATASET_SHAPES[cfg.dataset]["nnz"]
+                idx, y = synth.synth_onehot(self.spec.rows_per_part, cfg.n_cols, nnz, cfg.seed or 0, p, task, 0, self.dev)
+                return self._csr(idx), y
+            X, y = synth.synth_gmm(self.spec.rows_per_part, cfg.n_cols, cfg.seed or 0, p, task, self.dev)
             return X[:, :cfg.n_cols], y
-        X = torch.as_tensor(np.asarray(self.data.partition(p).todense() if self.data.is_sparse
-                                       else self.data.partition(p)), dtype=torch.float32, device=self.dev)
         y = torch.as_tensor(self.data.labels(p), dtype=torch.float32, device=self.dev)
+        if self.data.is_sparse:
+            return self._csr(torch.from_numpy(np.ascontiguousarray(self.data.ell(p))).to(self.dev)), y
+        X = torch.as_tensor(np.asarray(self.data.partition(p)), dtype=torch.float32, device=self.dev)
         return X, y
 
     def launches_per_round(self) -> int:
@@ -78,6 +94,11 @@ class NcclBaselineEngine:
         self.ctx.barrier()
 
     def _grad(self, X, y, coeff):
+        if isinstance(X, tuple):                              # one-hot data: two cuSPARSE CSR matvecs
+            Xs, Xt = X
+            p = torch.mv(Xs, self.beta32)
+            r = -2.0 * (y - p) if self.model.name == "linear" else -y / (torch.exp(p * y) + 1.0)
+            return torch.mv(Xt, coeff * r)
         p = X @ self.beta32                                   # cuBLAS GEMV
         if self.model.name == "linear":
             r = -2.0 * (y - p)
