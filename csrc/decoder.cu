@@ -279,7 +279,18 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
         for (int c4 = blockIdx.x * DEC_THREADS + tid; c4 < d4; c4 += gridDim.x * DEC_THREADS) {
             double g[4] = {0.0, 0.0, 0.0, 0.0};
             int q = 0;
-            for (; q + 4 <= nsrc; q += 4) {            // four loads in flight, summed in source order
+            for (; q + 8 <= nsrc; q += 8) {            // eight loads in flight, summed in source order
+                float4 t[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) t[u] = __ldcg(reinterpret_cast<const float4*>(s_src[q + u]) + c4);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const double a = s_wt[q + u];
+                    g[0] += a * (double)t[u].x; g[1] += a * (double)t[u].y;
+                    g[2] += a * (double)t[u].z; g[3] += a * (double)t[u].w;
+                }
+            }
+            for (; q + 4 <= nsrc; q += 4) {
                 float4 t[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) t[u] = __ldcg(reinterpret_cast<const float4*>(s_src[q + u]) + c4);
@@ -379,10 +390,13 @@ __global__ void publish_flag_kernel(const eh_decoder_desc D, const int round) {
 
 extern "C" size_t eh_decoder_scratch_bytes(void) { return sizeof(eh::DecScratch); }
 
-// CTAs (= SMs to reserve) a decoder for d_pad parameters wants: 2048 float4 columns per CTA, 1..16
+// CTAs (= SMs to reserve) a decoder for d_pad parameters wants: 2048 float4 columns per CTA, 1..16 (up to 32 for
+// parameter vectors beyond 128 K floats, e.g. the Amazon shape, whose rounds are bound by the decode of ~1 MB messages
+// and whose gradient kernels are small)
 extern "C" int eh_decoder_ctas(int d_pad) {
     int c = (d_pad / 4 + 4 * eh::DEC_THREADS - 1) / (4 * eh::DEC_THREADS);
-    return c < 1 ? 1 : (c > 16 ? 16 : c);
+    const int cap = d_pad > 131072 ? 32 : 16;
+    return c < 1 ? 1 : (c > cap ? cap : c);
 }
 
 static int check_desc(const eh_decoder_desc* D) {
