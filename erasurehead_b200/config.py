@@ -31,7 +31,9 @@ USAGE = ("Usage: python main.py " + " ".join(POSITIONALS) +
          " [--rounds=R --alpha=A --eta0=E --lr-schedule=const|t0decay|expdecay --seed=S "
          "--delay-scale=SEC --delay-mode=exp|fixed|dead|none --gpus=N --synthetic "
          "--model=logistic|linear|softmax --classes=C --compat --output-dir=DIR "
-         "--checkpoint-every=K --resume=PATH --eval=full|none --metrics-jsonl=PATH]")
+         "--checkpoint-every=K --resume=PATH --eval=full|none --metrics-jsonl=PATH "
+         "--synthetic-nnz=K --init=scheme|zeros|randn --dtype=fp32|bf16 --decoder=concurrent|inline --abandon "
+         "--beta-push=p2p|multicast --decode=auto|table|solve --cuda-graph --debug-poison]")
 
 SCHEMES = ("naive", "coded", "replication", "avoidstragg", "approx",
            "partial_coded", "partial_replication")

@@ -147,3 +147,20 @@ def test_predict_helpers_host():
     assert np.allclose(predict.predict_proba(X, B[0]), 1 / (1 + np.exp(-X @ B[0])))
     assert set(np.unique(predict.predict_label(X, B[0]))) <= {-1.0, 1.0}
     assert predict.predict_class(X, rng.randn(5, 4)).shape == (20,)
+
+
+def test_cli_synthetic_onehot_shape_softmax_without_files_or_gpu(tmp_path, capsys):
+    """--synthetic with is_real=1: one-hot data of a dataset shape (here a small custom one via --synthetic-nnz),
+    multi-class model, straight from the 13 positionals; on a machine without a GPU the oracle runs it."""
+    from erasurehead_b200 import cli
+    from erasurehead_b200.config import parse_argv
+    args = ["7", "1200", "400", str(tmp_path) + "/", "1", "myshape", "1", "2", "0", "3", "3", "0", "AGD",
+            "--synthetic", "--synthetic-nnz=9", "--model=softmax", "--classes=4", "--rounds=6", "--gpus=-1",
+            "--init=zeros", "--eta0=1.0", "--quiet", "--abandon", "--decoder=inline"]
+    out = cli.run(parse_argv(args))
+    ev = out["evaluation"]
+    assert out["result"].betaset.shape == (6, 400, 4)
+    assert np.all(np.isfinite(ev.training_loss)) and ev.training_loss[-1] < ev.training_loss[0]
+    import pytest
+    with pytest.raises(ValueError, match="synthetic-nnz"):
+        cli.run(parse_argv(args[:5] + ["unknown-shape"] + args[6:14] + ["--gpus=-1", "--quiet"]))
