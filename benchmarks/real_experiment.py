@@ -71,7 +71,15 @@ def run_one(ctx, dataset, scheme, delay, rounds, model=None, classes=1, impl="ou
     ev = eng.evaluate(res)
     rec = None
     if ctx.is_root:
-        rec = {"dataset": dataset, "rows": sh["n_rows"], "cols": sh["n_cols"], "nnz": sh["nnz"], "scheme": scheme,
+        # split of a round from the device stamps: parameter flag -> completion of the last message the stop rule
+        # needed -> its consumption by the decoder -> end of decode / update / push
+        used = res.worker_timeset >= 0
+        last_done = np.array([res.done[r][used[r]].max() if used[r].any() else np.nan for r in range(rounds)])
+        last_arr = np.array([res.worker_timeset[r][used[r]].max() if used[r].any() else np.nan for r in range(rounds)])
+        rec = {"split_ms": {"until_last_needed_message_complete": float(np.nanmean(last_done[3:]) * 1e3),
+                            "until_consumed": float(np.nanmean((last_arr - last_done)[3:]) * 1e3),
+                            "decode_update_push": float(np.nanmean((res.timeset - last_arr)[3:]) * 1e3)},
+               "dataset": dataset, "rows": sh["n_rows"], "cols": sh["n_cols"], "nnz": sh["nnz"], "scheme": scheme,
                "model": eng.model.name + (f"-{classes}" if classes > 1 else ""), "n_workers": N_WORKERS, "s": s,
                "n_collect": K if scheme == "approx" else None, "P": P if scheme.startswith("partial") else None,
                "gpus": ctx.world, "delay": {"none": "none", "scaled": "exp(5 ms)", "stock": "exp(0.5 s)"}[delay],

@@ -390,11 +390,12 @@ __global__ void publish_flag_kernel(const eh_decoder_desc D, const int round) {
 
 extern "C" size_t eh_decoder_scratch_bytes(void) { return sizeof(eh::DecScratch); }
 
-// CTAs (= SMs to reserve) a decoder for d_pad parameters wants: 2048 float4 columns per CTA, 1..16 (up to 32 for
-// parameter vectors beyond 128 K floats, e.g. the Amazon shape, whose rounds are bound by the decode of ~1 MB messages
-// and whose gradient kernels are small)
+// CTAs (= SMs to reserve) a decoder for d_pad parameters wants: one float4 column per thread (the decode is a chain
+// of dependent memory rounds per column, so columns per thread cost latency, not bandwidth), 1..16 CTAs, up to 32
+// for parameter vectors beyond 128 K floats (the Amazon shape: rounds are bound by the decode of ~1 MB messages
+// and the gradient kernels are small)
 extern "C" int eh_decoder_ctas(int d_pad) {
-    int c = (d_pad / 4 + 4 * eh::DEC_THREADS - 1) / (4 * eh::DEC_THREADS);
+    int c = (d_pad / 4 + eh::DEC_THREADS - 1) / eh::DEC_THREADS;
     const int cap = d_pad > 131072 ? 32 : 16;
     return c < 1 ? 1 : (c > cap ? cap : c);
 }
