@@ -23,6 +23,9 @@ KW = {
     "partial_replication": dict(n=4, s=1, P=4, rows=12 * 160), "sparse": dict(s=1, k=6, rows=8 * 120, d=700),
     "softmax": dict(s=1, k=6, rows=8 * 256, d=96, model="softmax", classes=5, eta0=0.5),
     "softmax_bf16": dict(s=1, k=6, rows=8 * 256, d=96, model="softmax", classes=5, eta0=0.5, dtype="bf16"),
+    # multi-column model on one-hot features (csrc/grad_ell_mc.cu) and dense workers that abandon decided rounds
+    "sparse_softmax": dict(s=1, k=6, rows=8 * 150, d=700, model="softmax", classes=5, eta0=0.5),
+    "abandon": dict(s=1, k=5, abandon=True),
 }
 
 
@@ -40,7 +43,7 @@ def main():
     bad = 0
     for name in sys.argv[2:]:
         kw = dict(KW[name])
-        scheme = "approx" if name in ("sparse", "softmax", "softmax_bf16") else name
+        scheme = "approx" if name in ("sparse", "softmax", "softmax_bf16", "sparse_softmax", "abandon") else name
         n, s, P, k = kw.pop("n", 8), kw.pop("s", 1), kw.pop("P", 0), kw.pop("k", 0)
         rows, d = kw.pop("rows", 1920), kw.pop("d", 48)
         ic, pp, cv = triple_from_scheme(scheme, P)
@@ -50,6 +53,9 @@ def main():
         if name == "sparse":
             cfg.is_real = 1
             data = generate_onehot(rows, d, 13, 8, seed=2)
+        elif name == "sparse_softmax":
+            cfg.is_real = 1
+            data = generate_onehot(rows, d, 13, 8, seed=2, task="softmax", classes=5)
         elif name.startswith("softmax"):
             data = generate_gmm(rows, d, cfg.n_partitions, seed=1, task="softmax", classes=5)
             if name == "softmax_bf16":                   # the oracle sees the same bf16-rounded features
@@ -63,7 +69,7 @@ def main():
         if ctx.is_root:
             ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0, model=eng.model)
             err = np.abs(res.betaset - ref.betaset).max() / max(1.0, np.abs(ref.betaset).max())
-            ok = (err <= ({"softmax": 5e-3, "softmax_bf16": 5e-3}.get(name, 1e-3)) and np.array_equal(res.n_collected, ref.n_collected)
+            ok = (err <= ({"softmax": 5e-3, "softmax_bf16": 5e-3, "sparse_softmax": 5e-3}.get(name, 1e-3)) and np.array_equal(res.n_collected, ref.n_collected)
                   and np.array_equal(res.worker_timeset >= 0, ref.worker_timeset >= 0))
             print(f"[mp_engine_check] {name}: world={ctx.world} device={ctx.device} rel_err={err:.2e} "
                   f"round_ms={res.timeset.mean() * 1e3:.2f} {'OK' if ok else 'MISMATCH'}", flush=True)

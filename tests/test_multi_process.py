@@ -8,7 +8,7 @@ import pytest
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ALL = ["naive", "coded", "replication", "avoidstragg", "approx", "partial_coded", "partial_replication", "sparse",
-       "softmax", "softmax_bf16"]
+       "softmax", "softmax_bf16", "sparse_softmax", "abandon"]
 
 
 def _free_port():
@@ -27,9 +27,9 @@ def _torchrun(nproc, device, schemes, timeout=300, extra_env=None):
 
 
 def test_two_process_gloo_cpu():
-    rc, out = _torchrun(2, "cpu", ["approx", "coded", "partial_coded", "softmax"])
+    rc, out = _torchrun(2, "cpu", ["approx", "coded", "partial_coded", "softmax", "sparse_softmax"])
     assert rc == 0, out[-3000:]
-    assert out.count("OK") == 4
+    assert out.count("OK") == 5
 
 
 def _gpu_count():
