@@ -100,18 +100,35 @@ class RoundPlan(C.Structure):
                 ("dec_stream", C.c_void_p), ("ev_fork", C.c_void_p), ("ev_join", C.c_void_p)]
 
 
+def _source_hash() -> str:
+    """SHA-1 over the native sources and the public header (what the binary was built from)."""
+    import hashlib
+    h = hashlib.sha1()
+    files = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".sh")))
+    files.append(os.path.join(ROOT, "include", "erasurehead.h"))
+    for f in files:
+        h.update(os.path.basename(f).encode())
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every ``csrc/*.cu`` for sm_100a into ``liberasurehead.so`` (no GPU needed)."""
-    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
-    srcs.append(os.path.join(ROOT, "include", "erasurehead.h"))
-    stale = force or not os.path.exists(LIB_PATH) or any(
-        os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs)
+    """Compile every ``csrc/*.cu`` for sm_100a into ``liberasurehead.so`` (no GPU needed).  The library is
+    rebuilt when it is missing or when the sources differ from the ones it was built from -- judged by a content
+    hash kept next to it, not by file times (a copied tree, e.g. on a GPU box, has arbitrary times)."""
+    stamp = LIB_PATH + ".srchash"
+    want = _source_hash()
+    have = open(stamp).read().strip() if os.path.exists(stamp) else ""
+    stale = force or not os.path.exists(LIB_PATH) or have != want
     if stale:
         proc = subprocess.run(["bash", os.path.join(CSRC, "build.sh")], capture_output=True, text=True)
         if verbose or proc.returncode:
             print(proc.stdout[-4000:], proc.stderr[-4000:])
         if proc.returncode:
             raise EhError("nvcc build of liberasurehead.so failed")
+        with open(stamp, "w") as f:
+            f.write(want + "\n")
     return LIB_PATH
 
 
