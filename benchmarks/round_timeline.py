@@ -20,7 +20,6 @@ import sys
 
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 
-import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 from erasurehead_b200 import Engine, RunConfig, triple_from_scheme  # noqa: E402

@@ -15,7 +15,9 @@
 // scatter is `red.global.add.v4.f32` (two 16-byte L2 reductions per one); a lane keeps the last
 // feature it touched and its accumulated residual vector in registers and only flushes when
 // the feature changes, which removes the always-on bias feature (every row) from the atomic
-// traffic altogether and shortens the runs on the popular levels.  The accumulation vector
+// traffic altogether and shortens the runs on the popular levels; single hits go through a
+// per-CTA two-way table of fixed-point accumulators in shared memory (see HotTable below) so that
+// the popular levels do not serialise as same-address L2 reductions.  The accumulation vector
 // lives in scratch (one per batched message), is zeroed, filled and shipped -- to local or peer
 // memory, followed by the arrival record -- by this one cooperative kernel.
 #include <stdlib.h>
