@@ -553,14 +553,38 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
     uint32_t gen = 0;
     grid_barrier(&p.hdr->barrier, gen);
 
-    // ordered reduction per message: CTA bl of the message owns a contiguous column range
+    // ordered reduction per message: CTA bl of the message owns a contiguous column range.  Eight thread groups
+    // each add every eighth partial of a column (adjacent threads = adjacent columns: coalesced), the eight
+    // sub-sums meet in shared memory (the accumulators are no longer needed) and are added in a fixed order --
+    // a single thread walking all Gj partials of its column was a chain of up to 148 loads
     const int chunk = (p.d + Gj - 1) / Gj;
     const int c0 = bl * chunk, c1 = min(p.d, c0 + chunk);
     float* out = p.job_out[jb];
-    for (int c = c0 + tid; c < c1; c += GFX_THREADS) {
+    constexpr int SUB = 8, CW = GFX_THREADS / SUB;
+    float* sred = ges_smem;
+    const int sub = tid / CW, cx = tid % CW;
+    if (Gj < 64) {
+        // few partials per column (batched messages): one thread per column is the shorter path
+        for (int c = c0 + tid; c < c1; c += GFX_THREADS) {
+            float t = 0.f;
+            for (int g = b0; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
+            out[c] = t;
+        }
+    } else
+    for (int cb = c0; cb < c1; cb += CW) {
+        const int c = cb + cx;
         float t = 0.f;
-        for (int g = b0; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
-        out[c] = t;
+        if (c < c1)
+            for (int g = b0 + sub; g < b0 + Gj; g += SUB) t += __ldcg(partials + (size_t)g * p.d + c);
+        sred[sub * CW + cx] = t;
+        __syncthreads();
+        if (sub == 0 && c < c1) {
+            float u = sred[cx];
+#pragma unroll
+            for (int q = 1; q < SUB; ++q) u += sred[q * CW + cx];
+            out[c] = u;
+        }
+        __syncthreads();
     }
     __syncthreads();
     if (tid == 0) {
