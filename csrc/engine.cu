@@ -33,9 +33,9 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
         const int par = round & 1;
         const uint32_t stamp = (uint32_t)round + 1u;
         // dense single-vector messages of one shape are batched into one launch (<= 8 messages,
-        // <= 32 partitions), and so are one-hot messages; multi-column messages get their own kernels
+        // <= 32 partitions), and so are one-hot messages (<= 16 messages, <= 64 partitions); multi-column messages get their own kernels
         eh_grad_job batch[8];
-        eh_grad_ell_job ebatch[8];
+        eh_grad_ell_job ebatch[16];
         int nb = 0, nb_segs = 0, ne = 0, ne_segs = 0, e_classes = 0;     // e_classes > 0: the one-hot batch is multi-column
         auto flush = [&]() -> int {
             int rc = EH_OK;
@@ -112,7 +112,7 @@ extern "C" int eh_run_rounds(const eh_round_plan* plan, int first_round, int n_r
                 j.n_segs = wj.n_segs; j.rows_per_seg = wj.rows_per_seg; j.d = wj.d; j.nnz = wj.ld_or_nnz;
                 j.model = wj.model; j.bias_col = wj.bias_col; j.stamp = stamp; j.timeout_ns = plan->timeout_ns;
                 const int cls = (wj.sparse == 5) ? wj.classes : 0;
-                const bool fits = nb == 0 && ne < 8 && ne_segs + j.n_segs <= 32 && (ne == 0 || cls == e_classes) &&
+                const bool fits = nb == 0 && ne < 16 && ne_segs + j.n_segs <= 64 && (ne == 0 || cls == e_classes) &&
                                   (ne == 0 || (ebatch[0].d == j.d && ebatch[0].nnz == j.nnz &&
                                                ebatch[0].rows_per_seg == j.rows_per_seg && ebatch[0].model == j.model &&
                                                ebatch[0].bias_col == j.bias_col));

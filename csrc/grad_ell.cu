@@ -22,8 +22,8 @@ namespace eh {
 
 constexpr int GE_THREADS = 512;
 constexpr int GE_TABLE = 2048;                 // per-CTA hot-column accumulators (direct-mapped)
-constexpr int GE_MAX_SEGS = 32;                // partitions over all batched messages
-constexpr int GE_MAX_JOBS = 8;                 // messages batched into one launch (shared-memory variant)
+constexpr int GE_MAX_SEGS = 64;                // partitions over all batched messages
+constexpr int GE_MAX_JOBS = 16;                 // messages batched into one launch (shared-memory variant)
 constexpr uint32_t GE_GO = 1, GE_SKIP = 2;
 
 struct EllScratchHdr {

@@ -28,8 +28,8 @@ namespace eh {
 
 constexpr int GEM_THREADS = 512;
 constexpr int GEM_CP = 8;                       // padded classes per feature
-constexpr int GEM_MAX_SEGS = 32;
-constexpr int GEM_MAX_JOBS = 8;
+constexpr int GEM_MAX_SEGS = 64;
+constexpr int GEM_MAX_JOBS = 16;
 constexpr uint32_t GEM_GO = 1, GEM_SKIP = 2;
 
 struct EllMcHdr {

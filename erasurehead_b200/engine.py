@@ -393,11 +393,11 @@ class Engine:
         if not self.on_gpu:
             return 0
         k = 0
-        if self.mc and self.sparse:                               # batched 8 messages / 32 partitions per launch
+        if self.mc and self.sparse:                               # batched 16 messages / 64 partitions per launch
             nb = segs = 0
             for q in range(self.n_jobs):
                 ns = self._jobs[q].n_segs
-                if nb and (nb == 8 or segs + ns > 32):
+                if nb and (nb == 16 or segs + ns > 64):
                     k += 1
                     nb = segs = 0
                 nb += 1
@@ -407,11 +407,11 @@ class Engine:
             # one launch per message for the one-pass kernels, else wait + 2 per partition + ship + flag
             one_pass = self.bf16 or _pad32(self.cfg.n_cols) <= 1024
             k = sum(1 if one_pass else 2 * self._jobs[q].n_segs + 3 for q in range(self.n_jobs))
-        elif self.sparse:                                          # batched 8 messages / 32 partitions per launch
+        elif self.sparse:                                          # batched 16 messages / 64 partitions per launch
             nb = segs = 0
             for q in range(self.n_jobs):
                 ns = self._jobs[q].n_segs
-                if nb and (nb == 8 or segs + ns > 32):
+                if nb and (nb == 16 or segs + ns > 64):
                     k += 1
                     nb = segs = 0
                 nb += 1

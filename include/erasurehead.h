@@ -150,9 +150,9 @@ typedef struct eh_grad_ell_job {
 
 size_t eh_grad_ell_scratch_bytes(int d);
 int eh_grad_ell(const eh_grad_ell_job* job, void* d_scratch, size_t scratch_bytes, void* stream);
-/* Up to 8 one-hot messages of identical shape (same d, nnz, rows_per_seg, model, bias_col, parameters, stamp;
- * at most 32 partitions in total) in ONE launch when the gradient fits in shared memory (CTA ranges per
- * message); otherwise one launch per message. */
+/* Up to 16 one-hot messages of identical shape (same d, nnz, rows_per_seg, model, bias_col, parameters, stamp;
+ * at most 64 partitions in total) in ONE launch: CTA ranges per message, per-CTA partial gradients in shared
+ * memory when the gradient fits, else one accumulation vector per message in scratch. */
 int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* d_scratch, size_t scratch_bytes, void* stream);
 
 /* Multi-column model on one-hot ELL features: softmax regression with C <= 8 classes (model 2, labels
@@ -161,7 +161,7 @@ int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* d_scratch, 
  * arrange_real_data.py:154-156, so the model has no reference counterpart).  Jobs are eh_grad_ell_job
  * with d_beta / d_out in COLUMN-major layout W[d][8] (eh_grad_ell_mc_padded_classes() floats per
  * feature: one 32-byte sector) -- a flat vector of 8 d floats for the decoder; bias_col is ignored.
- * Up to 8 messages of one shape per launch (CTA ranges per message, one accumulation vector each in
+ * Up to 16 messages of one shape per launch (CTA ranges per message, one accumulation vector each in
  * scratch >= eh_grad_ell_mc_scratch_bytes(d)); scatter by 16-byte L2 reductions with a per-lane
  * run-length cache (csrc/grad_ell_mc.cu). */
 int eh_grad_ell_mc_padded_classes(void);
