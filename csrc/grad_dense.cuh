@@ -94,7 +94,30 @@ __device__ __forceinline__ void reduce_and_ship(const GradParams& p, unsigned ch
     // a CTA that saw the round end while streaming raised hdr->aborted before the barrier: nothing is shipped
     const bool aborted = p.abandon && ld_acquire_gpu(&p.hdr->aborted) != 0u;
 
-    if (warp < GD_CONSUMER_WARPS && !aborted) {
+    if (warp < GD_CONSUMER_WARPS && !aborted && jv.Gj <= GD_CONSUMER_WARPS) {
+        // a message that runs on a handful of CTAs (small partitions): every warp reduces its own column groups --
+        // the eight-warp split below would leave most warps idle and pay two block barriers per group
+        const int ld4 = p.ld >> 2;
+        const int n_groups = (ld4 + 31) / 32;
+        for (int grp = jv.bl * GD_CONSUMER_WARPS + warp; grp < n_groups; grp += jv.Gj * GD_CONSUMER_WARPS) {
+            const int c4 = grp * 32 + lane;
+            if (c4 < ld4) {
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int row = jv.b0; row < jv.b0 + jv.Gj; ++row) {
+                    const float4 u = __ldcg(reinterpret_cast<const float4*>(p.partials + (size_t)row * p.ldp) + c4);
+                    t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+                }
+                const int c = c4 * 4;
+                if (c + 3 < p.d) {
+                    *reinterpret_cast<float4*>(out + c) = t;
+                } else {
+                    if (c + 0 < p.d) out[c + 0] = t.x;
+                    if (c + 1 < p.d) out[c + 1] = t.y;
+                    if (c + 2 < p.d) out[c + 2] = t.z;
+                }
+            }
+        }
+    } else if (warp < GD_CONSUMER_WARPS && !aborted) {
         const int ld4 = p.ld >> 2;
         const int n_groups = (ld4 + 31) / 32;                 // 32 float4 columns per group
         float4* sred = reinterpret_cast<float4*>(smem_raw);   // [8][32] float4, ring is idle now
