@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(GE_THREADS) grad_ell_kernel(const EllParams p)
         const int lr = (int)(row % p.rows_per_seg);
         const int32_t* ri = p.seg_idx[sg] + (size_t)lr * p.nnz;
         float s = 0.f;
-        for (int k = lane; k < p.nnz; k += 32) s += __ldcg(p.beta + __ldg(ri + k));
+        for (int k = lane; k < p.nnz; k += 32) s += p.beta[__ldg(ri + k)];          // L1-cacheable: popular features stay on the SM
         s = warp_sum(s);
         const float rs = p.coeff[sg] * ell_residual(p.model, s, __ldg(p.seg_y[sg] + lr));
         for (int k = lane; k < p.nnz; k += 32) {
@@ -475,7 +475,7 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
     };
     auto gather = [&](int c) -> float {
         if (BETA_IN_SMEM) return bsm[c];
-        return c < dummy ? __ldcg(p.beta + c) : 0.f;
+        return c < dummy ? p.beta[c] : 0.f;               // L1-cacheable (nothing of beta was read before the flag)
     };
     auto process = [&](const RowSet& R, int row0) {
         float s[RW];

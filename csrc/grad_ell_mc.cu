@@ -107,17 +107,14 @@ __device__ __forceinline__ void scatter(float* g, const HotTable& T, int col, co
     red_add_v4(g + (size_t)col * GEM_CP, v[0], v[1], v[2], v[3]);
     red_add_v4(g + (size_t)col * GEM_CP + 4, v[4], v[5], v[6], v[7]);
 }
+// A run of n rows is one addend of magnitude <= n * bound; the sum of all addends of a CTA is still bounded by its
+// row count times the bound, so runs of any length (the bias feature: every row of a warp) fit the fixed-point slot.
 __device__ __forceinline__ void run_flush(float* g, const HotTable& T, LaneRun& R) {
-    if (R.col >= 0) {
-        // a run longer than a few rows (the bias feature: every row) would overflow the fixed-point slot: straight to L2
-        red_add_v4(g + (size_t)R.col * GEM_CP, R.v[0], R.v[1], R.v[2], R.v[3]);
-        red_add_v4(g + (size_t)R.col * GEM_CP + 4, R.v[4], R.v[5], R.v[6], R.v[7]);
-    }
+    if (R.col >= 0) scatter(g, T, R.col, R.v);
 }
 __device__ __forceinline__ void run_add(float* g, const HotTable& T, LaneRun& R, int col, const float (&r)[GEM_CP]) {
     if (col != R.col) {
-        if (R.col >= 0 && R.n == 1) scatter(g, T, R.col, R.v);        // a single hit: through the table
-        else run_flush(g, T, R);
+        run_flush(g, T, R);
         R.n = 0;
         R.col = col;
 #pragma unroll
@@ -232,16 +229,16 @@ __global__ void __launch_bounds__(GEM_THREADS) grad_ell_mc_kernel(const EllMcPar
 #pragma unroll
         for (int c = 0; c < GEM_CP; ++c) lg[c] = 0.f;
         if (c0 >= 0) {
-            const float4 a = __ldcg(W4 + (size_t)c0 * 2), bb = __ldcg(W4 + (size_t)c0 * 2 + 1);
+            const float4 a = W4[(size_t)c0 * 2], bb = W4[(size_t)c0 * 2 + 1];       // L1-cacheable: popular features stay on the SM
             lg[0] = a.x; lg[1] = a.y; lg[2] = a.z; lg[3] = a.w; lg[4] = bb.x; lg[5] = bb.y; lg[6] = bb.z; lg[7] = bb.w;
         }
         if (c1 >= 0) {
-            const float4 a = __ldcg(W4 + (size_t)c1 * 2), bb = __ldcg(W4 + (size_t)c1 * 2 + 1);
+            const float4 a = W4[(size_t)c1 * 2], bb = W4[(size_t)c1 * 2 + 1];       // L1-cacheable: popular features stay on the SM
             lg[0] += a.x; lg[1] += a.y; lg[2] += a.z; lg[3] += a.w; lg[4] += bb.x; lg[5] += bb.y; lg[6] += bb.z; lg[7] += bb.w;
         }
         for (int k = lane + 64; k < nnz; k += 32) {             // rows with more than 64 ones (not the named shapes)
             const int c = __ldg(ri + k);
-            const float4 a = __ldcg(W4 + (size_t)c * 2), bb = __ldcg(W4 + (size_t)c * 2 + 1);
+            const float4 a = W4[(size_t)c * 2], bb = W4[(size_t)c * 2 + 1];       // L1-cacheable: popular features stay on the SM
             lg[0] += a.x; lg[1] += a.y; lg[2] += a.z; lg[3] += a.w; lg[4] += bb.x; lg[5] += bb.y; lg[6] += bb.z; lg[7] += bb.w;
         }
         // 8 sums over 32 lanes: halves trade classes (0..3 <-> 4..7), quarters (pairs), eighths (singles)
