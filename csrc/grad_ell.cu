@@ -348,10 +348,11 @@ constexpr int GFX_THREADS = 1024;            // fixed-point variant: 32 warps pe
 template <bool BETA_IN_SMEM, bool WIDE>
 __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllParams p, float* __restrict__ partials) {
     extern __shared__ __align__(16) float ges_smem[];
-    // hi[d + 1], lo[d + 1] accumulator words (separate arrays: consecutive columns fall into consecutive banks),
-    // then [d + 1] parameters; slot d is a dummy column that absorbs the padding lanes (a row of 55 ones
-    // occupies 64 lanes) so the hot loop has no branches
-    const int dd = ((p.d + 1) + 3) & ~3;
+    // hi[d + 32], lo[d + 32] accumulator words (separate arrays: consecutive columns fall into consecutive banks),
+    // then [d + 32] parameters; slots d .. d+31 are dummy columns, one per lane, that absorb the padding lanes (a row
+    // of 55 ones occupies 64 lanes) so the hot loop has no branches -- one per lane because nine padding lanes adding
+    // to ONE dummy word were a nine-way same-address conflict in every second scatter instruction
+    const int dd = ((p.d + 32) + 3) & ~3;
     int* acc_hi = reinterpret_cast<int*>(ges_smem);
     int* acc_lo = acc_hi + dd;
     float* bsm = ges_smem + 2 * dd;
@@ -360,7 +361,7 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int G = gridDim.x, b = blockIdx.x;
 
-    for (int c = tid; c <= p.d; c += GFX_THREADS) { acc_hi[c] = 0; acc_lo[c] = 0; }
+    for (int c = tid; c < p.d + 32; c += GFX_THREADS) { acc_hi[c] = 0; acc_lo[c] = 0; }
 
     // which batched message this CTA works for
     int jb = 0;
@@ -373,7 +374,7 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
     const int gwarp = bl * (GFX_THREADS / 32) + warp;
     const int nwarps = Gj * (GFX_THREADS / 32);
     constexpr int RW = 4;                      // rows per warp and step
-    const int nnz = p.nnz, dummy = p.d;
+    const int nnz = p.nnz, dummy = p.d + lane;
 
     // |y|max over this CTA's rows and |coeff|max over the message's partitions (independent of the parameters)
     float ymax = 0.f, cmax = 0.f;
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
             bsm[c] = t;
             bmax = fmaxf(bmax, fabsf(t));
         }
-        if (tid == 0) bsm[dummy] = 0.f;
+        if (tid < 32) bsm[p.d + tid] = 0.f;
     } else if (p.model != EH_MODEL_LOGISTIC) {
         for (int c = tid; c < p.d; c += GFX_THREADS) bmax = fmaxf(bmax, fabsf(__ldcg(p.beta + c)));
     }
@@ -457,6 +458,7 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
         const int32_t* rip[RW];
     };
     const bool l0 = lane < nnz, l1 = lane + 32 < nnz;
+    const bool two = nnz > 32;                 // rows of at most 32 ones (KC-House: 19) need no second lane pass
     // (sg, lr) = partition and local row of the first row of a set, advanced without divisions
     auto load_rows = [&](int row0, int sg0, int lr0, RowSet& R) {
 #pragma unroll
@@ -468,20 +470,21 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
             const int32_t* ri = p.seg_idx[sg] + (size_t)lr * nnz;
             R.rip[r] = ri;
             R.c0[r] = (valid && l0) ? __ldg(ri + lane) : dummy;
-            R.c1[r] = (valid && l1) ? __ldg(ri + lane + 32) : dummy;
+            R.c1[r] = (two && valid && l1) ? __ldg(ri + lane + 32) : dummy;
             R.yv[r] = __ldg(p.seg_y[sg] + lr);
             R.cf[r] = valid ? p.coeff[sg] : 0.f;
         }
     };
     auto gather = [&](int c) -> float {
         if (BETA_IN_SMEM) return bsm[c];
-        return c < dummy ? p.beta[c] : 0.f;               // L1-cacheable (nothing of beta was read before the flag)
+        return c < p.d ? p.beta[c] : 0.f;                 // L1-cacheable (nothing of beta was read before the flag)
     };
     auto process = [&](const RowSet& R, int row0) {
         float s[RW];
 #pragma unroll
         for (int r = 0; r < RW; ++r) {
-            float t = gather(R.c0[r]) + gather(R.c1[r]);
+            float t = gather(R.c0[r]);
+            if (two) t += gather(R.c1[r]);
             if (WIDE) {
                 if (row0 + r < job_rows)
                     for (int k = lane + 64; k < nnz; k += 32) t += gather(__ldg(R.rip[r] + k));
@@ -510,7 +513,7 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
             const int vh = v >> LB;
             const int vl = (int)((unsigned)v & lo_mask);
             atomicAdd(acc_hi + R.c0[r], vh); atomicAdd(acc_lo + R.c0[r], vl);
-            atomicAdd(acc_hi + R.c1[r], vh); atomicAdd(acc_lo + R.c1[r], vl);
+            if (two) { atomicAdd(acc_hi + R.c1[r], vh); atomicAdd(acc_lo + R.c1[r], vl); }
             if (WIDE) {
                 if (row0 + r < job_rows)
                     for (int k = lane + 64; k < nnz; k += 32) {
@@ -665,7 +668,7 @@ extern "C" int eh_grad_ell_multi(const eh_grad_ell_job* jobs, int n_jobs, void* 
     p.model = j->model; p.bias_col = j->bias_col; p.stamp = j->stamp; p.seq = next_launch_seq();
     p.timeout_ns = j->timeout_ns ? j->timeout_ns : 30ull * 1000000000ull;
     // fixed-point variant (native integer shared-memory atomics) when two words per column fit
-    const size_t fx_col_bytes = (size_t)(((j->d + 1) + 3) & ~3) * sizeof(float);      // one word per column incl. the dummy
+    const size_t fx_col_bytes = (size_t)(((j->d + 32) + 3) & ~3) * sizeof(float);     // one word per column incl. 32 dummies
     const bool fx_variant = smem_variant && 2 * fx_col_bytes <= GES_SMEM_LIMIT && getenv("EH_ELL_FLOAT_ATOMICS") == nullptr;
     if (smem_variant) {
         const bool both = fx_variant ? 3 * fx_col_bytes <= GES_SMEM_LIMIT : 2 * acc_bytes <= GES_SMEM_LIMIT;
