@@ -570,7 +570,15 @@ __global__ void __launch_bounds__(GFX_THREADS, 1) grad_ell_fx_kernel(const EllPa
         // few partials per column (batched messages): one thread per column is the shorter path
         for (int c = c0 + tid; c < c1; c += GFX_THREADS) {
             float t = 0.f;
-            for (int g = b0; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
+            int g = b0;
+            for (; g + 8 <= b0 + Gj; g += 8) {                    // eight loads in flight, added in CTA order
+                float u[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) u[q] = __ldcg(partials + (size_t)(g + q) * p.d + c);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) t += u[q];
+            }
+            for (; g < b0 + Gj; ++g) t += __ldcg(partials + (size_t)g * p.d + c);
             out[c] = t;
         }
     } else
