@@ -76,10 +76,13 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
         const uint64_t* delay = D.d_delay_ns + (size_t)r * n;
         Entry ent[2][EH_MAX_MSGS];                 // workers lane, lane+32 ; msgs
         uint64_t dl[2];
+        int grp_of[2];                             // FRC group of workers lane, lane + 32 (read once: a global load
+                                                   // per consumed arrival sat in the serial consumption loop)
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
             const int w = lane + 32 * q;
             dl[q] = (w < n) ? delay[w] : NEVER;
+            grp_of[q] = (w < n) ? D.d_group_of[w] : 0;
 #pragma unroll
             for (int m = 0; m < EH_MAX_MSGS; ++m) {
                 ent[q][m].ready = NEVER;
@@ -160,7 +163,7 @@ decoder_round_kernel(const eh_decoder_desc D, const int round, const int r) {
                     done_mask |= 1ull << w;
                     if (lane == 0) s_S[n_order] = w;
                     n_order += 1;
-                    const int g = D.d_group_of[w];
+                    const int g = __shfl_sync(0xffffffffu, (w & 32) ? grp_of[1] : grp_of[0], w & 31);
                     if (!((cov_mask >> g) & 1ull)) {
                         cov_mask |= 1ull << g;
                         cnt_groups += 1;
