@@ -89,6 +89,8 @@ if __name__ == "__main__":
     for w in a.which.split(","):
         if w == "rowwarp":
             dense(262144, 1024)
+        elif w == "dense4096":
+            dense(524288, 4096)             # one partition of the headline configuration
         elif w == "cluster":
             dense(16384, 16384)
         elif w == "bf16":
