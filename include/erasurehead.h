@@ -375,6 +375,13 @@ int eh_code_cyclic(const double* d_H, int n, int s, double* d_B, void* stream);
 int eh_code_decode_table(const double* d_B, int n, int s, const int32_t* d_missing,
                          int64_t n_patterns, double* d_A, void* stream);
 
+/* Native reader of the reference's dense text partitions (util.py:13-15 np.loadtxt of util.py:26-30 files):
+ * memory-mapped, parsed on all cores, float32 or float64 output with a caller-chosen row stride (host
+ * memory, e.g. the pinned staging buffer of a partition).  eh_text_shape counts rows (non-blank lines)
+ * and columns (numbers on the first line). */
+int eh_text_shape(const char* path, int64_t* rows, int64_t* cols);
+int eh_load_dense_text(const char* path, int64_t rows, int64_t cols, void* h_out, int64_t ld, int elem_bytes);
+
 /* One-hot feature construction (K15): idx[r,c] = offsets[c] + codes[r,c]; pair features as the
  * mixed-radix id of two label-encoded columns (arrange_real_data.py:41-64, util.py:49-55). */
 int eh_onehot_assemble(const long long* d_codes, const long long* d_offsets, int64_t rows, int cols,

@@ -164,3 +164,35 @@ def test_cli_synthetic_onehot_shape_softmax_without_files_or_gpu(tmp_path, capsy
     import pytest
     with pytest.raises(ValueError, match="synthetic-nnz"):
         cli.run(parse_argv(args[:5] + ["unknown-shape"] + args[6:14] + ["--gpus=-1", "--quiet"]))
+
+
+def test_native_text_reader_matches_numpy_bit_for_bit(tmp_path):
+    """csrc/textio.cu behind utils.io.load_data: correctly rounded decimals (17-digit shortest representations,
+    half-way cases, subnormals, infinities), float32 and float64 output, vectors, and a clear error on a ragged row."""
+    from erasurehead_b200.utils import io
+    rng = np.random.RandomState(0)
+    X = rng.standard_normal((700, 131)) * np.exp(rng.uniform(-40, 40, (700, 131)))
+    X[0, :4] = [0.0, -0.0, 1e308, 5e-324]
+    X[1, :3] = [123456789012345678901234.0, np.inf, -1.0]
+    p = str(tmp_path / "a.dat")
+    io.save_matrix(X, p)
+    try:
+        A = io._load_data_native(p)
+    except Exception as e:           # no nvcc / no library on this machine: the numpy path is the only one
+        import pytest
+        pytest.skip(f"native library unavailable: {e}")
+    assert np.array_equal(A, np.loadtxt(p)) and np.array_equal(A, X)
+    with np.errstate(over="ignore"):
+        assert np.array_equal(io._load_data_native(p, np.float32), X.astype(np.float32))
+    assert np.array_equal(io.load_data(p), X)                       # public entry point takes the native path (> 64 KB)
+    tricky = ["9007199254740993", "9007199254740992.5", "0.1", "1e23", "8.41e21", "2.2250738585072014e-308",
+              "1.7976931348623157e308", "4.35e-17", "123456789.123456789e5", "+3.5", "-.5", "7."]
+    q = str(tmp_path / "t.dat")
+    open(q, "w").write(("\n".join(tricky) + "\n") * 3000)
+    T = io._load_data_native(q)
+    assert T.shape == (len(tricky) * 3000,) and np.array_equal(T[:len(tricky)], np.array([float(v) for v in tricky]))
+    bad = str(tmp_path / "bad.dat")
+    open(bad, "w").write("1 2 3\n" * 5000 + "1 2\n")
+    import pytest
+    with pytest.raises(Exception, match="row 5001 does not hold exactly 3"):
+        io._load_data_native(bad)
