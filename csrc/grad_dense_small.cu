@@ -33,7 +33,7 @@ __global__ void __launch_bounds__(GD_THREADS, 1) grad_dense_rowwarp_kernel(const
     constexpr int RPW = 32 / LPR;                       // rows a warp processes concurrently
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int G = gridDim.x, b = blockIdx.x;
+    const int b = blockIdx.x;
     constexpr int EB = 16 / E;                          // bytes per element
     const uint32_t stage_bytes = (uint32_t)RB * p.ld * EB;
     unsigned char* stages = smem_raw;
