@@ -36,8 +36,13 @@ def run(cfg: RunConfig, data=None, ctx=None, out=None) -> Optional[dict]:
     out = out or sys.stdout
     ctx = ctx or init_distributed("cpu" if cfg.gpus < 0 else None)
     if data is None and not cfg.synthetic:
+        import numpy as np
+        on_gpu = ctx.device.type == "cuda"
+        # on GPUs every rank reads only the partition files of its own workers (the root one more at a time while it
+        # evaluates), as float32; the CPU oracle works on all of them in float64 like the reference
         data = load_dataset(cfg.data_dir, cfg.n_partitions, bool(cfg.is_real), cfg.n_cols,
-                            rows_per_part=cfg.n_rows // cfg.n_partitions)
+                            rows_per_part=cfg.n_rows // cfg.n_partitions, lazy=on_gpu,
+                            dtype=np.float32 if on_gpu else float)
     eng = Engine(cfg, data, ctx=ctx)
     say = (lambda *a: print(*a, file=out)) if ctx.is_root and not cfg.quiet else (lambda *a: None)
     say(BANNERS[cfg.scheme].format(s=cfg.n_stragglers, delay=cfg.add_delay))

@@ -88,15 +88,59 @@ def ell_to_csr(idx: np.ndarray, n_cols: int) -> csr_matrix:
                       shape=(rows, n_cols))
 
 
+class _LazyParts:
+    """Partition list that reads a file when it is first asked for and keeps only the last few in memory.
+
+    A reference worker loads its own s + 1 partition files and nothing else (approximate_coding.py:39-69); a rank of
+    this framework likewise touches only the partitions of its local workers (plus, on the root, one partition at a
+    time during evaluation), so loading all n files on every rank would multiply host memory and I/O by the number
+    of GPUs."""
+
+    def __init__(self, data_dir: str, n: int, is_real: bool, dtype, keep: int = 2):
+        self.data_dir, self.n, self.is_real, self.dtype, self.keep = data_dir, n, is_real, dtype, keep
+        self._cache = {}
+        self._order = []
+
+    def __len__(self):
+        return self.n
+
+    def _load(self, k: int):
+        if self.is_real:
+            return io.load_sparse_csr(os.path.join(self.data_dir, str(k + 1)))
+        return np.atleast_2d(io.load_data(os.path.join(self.data_dir, f"{k + 1}.dat"), dtype=self.dtype))
+
+    def __getitem__(self, k):
+        if isinstance(k, slice):
+            return [self[i] for i in range(*k.indices(self.n))]
+        if k < 0:
+            k += self.n
+        if not 0 <= k < self.n:
+            raise IndexError(k)
+        if k not in self._cache:
+            self._cache[k] = self._load(k)
+            self._order.append(k)
+            while len(self._order) > self.keep:
+                self._cache.pop(self._order.pop(0), None)
+        return self._cache[k]
+
+    def __iter__(self):
+        return (self[k] for k in range(self.n))
+
+
 def load_dataset(data_dir: str, n_partitions: int, is_real: bool, n_cols: int,
-                 rows_per_part: Optional[int] = None) -> Dataset:
-    """Read the reference directory layout (approximate_coding.py:39-69)."""
-    parts = []
-    for k in range(1, n_partitions + 1):
+                 rows_per_part: Optional[int] = None, lazy: bool = False, dtype=float) -> Dataset:
+    """Read the reference directory layout (approximate_coding.py:39-69).  ``lazy`` defers every partition file
+    until it is used (see :class:`_LazyParts`); ``dtype`` is the element type of dense partitions (float32 halves
+    the host memory when the data only feeds the GPU kernels, which store fp32 or bf16 anyway)."""
+    if lazy:
+        parts = _LazyParts(data_dir, n_partitions, is_real, dtype)
+    else:
+        parts = []
+    for k in range(1, n_partitions + 1 if not lazy else 1):
         if is_real:
             parts.append(io.load_sparse_csr(os.path.join(data_dir, str(k))))
         else:
-            parts.append(np.atleast_2d(io.load_data(os.path.join(data_dir, f"{k}.dat"))))
+            parts.append(np.atleast_2d(io.load_data(os.path.join(data_dir, f"{k}.dat"), dtype=dtype)))
     y = np.atleast_1d(io.load_data(os.path.join(data_dir, "label.dat")))
     y_test = np.atleast_1d(io.load_data(os.path.join(data_dir, "label_test.dat")))
     if is_real:

@@ -196,3 +196,23 @@ def test_native_text_reader_matches_numpy_bit_for_bit(tmp_path):
     import pytest
     with pytest.raises(Exception, match="row 5001 does not hold exactly 3"):
         io._load_data_native(bad)
+
+
+def test_lazy_dataset_reads_partitions_on_demand(tmp_path):
+    """load_dataset(lazy=True): a rank only reads the partition files it uses (and keeps the last two in memory);
+    float32 on request; same values as the eager reader."""
+    from erasurehead_b200.data import generate_gmm_to_disk, load_dataset
+    from erasurehead_b200.data.shapes import generate_onehot
+    out = generate_gmm_to_disk(5, 4 * 300, 40, str(tmp_path), 1, 0, 0, seed=3)
+    a = load_dataset(out, 4, False, 40)
+    b = load_dataset(out, 4, False, 40, lazy=True, dtype=np.float32)
+    assert b.n_partitions == 4 and not b.is_sparse and b.rows_per_part == 300
+    assert list(b.parts._cache) == [0]                       # is_sparse looked at partition 0 only
+    assert b.partition(2).dtype == np.float32 and np.allclose(a.partition(2), b.partition(2), atol=1e-6)
+    b.partition(3)
+    assert sorted(b.parts._cache) == [2, 3]
+    X, y = b.train_matrix(3)
+    assert X.shape == (900, 40) and np.allclose(X, np.vstack(a.parts[:3]), atol=1e-6)
+    generate_onehot(4 * 200, 500, 9, 4, seed=1).save(str(tmp_path / "oh") + "/")
+    c = load_dataset(str(tmp_path / "oh") + "/", 4, True, 500, lazy=True)
+    assert c.is_sparse and c.ell(3).shape == (200, 9) and c.labels(3).shape == (200,)
