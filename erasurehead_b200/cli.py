@@ -1,4 +1,4 @@
-"""Command-line driver with the reference's 13-positional contract (main.py:20-95).
+"""Command-line driver with the reference's 13-positional contract (main.py:20-94).
 
     python main.py n_procs n_rows n_cols input_dir is_real dataset is_coded n_stragglers \
                    partitions coded_ver num_collect add_delay update_rule [--key=value ...]
