@@ -269,7 +269,7 @@ class Engine:
         plan.lay = lay
         self._dec_stream = None
         if self.dec is not None and cfg.decoder == "concurrent":
-            lo, hi = torch.cuda.Stream.priority_range()          # (least, greatest) = (0, -N)
+            _, hi = torch.cuda.Stream.priority_range()          # (least, greatest) = (0, -N)
             self._dec_stream = torch.cuda.Stream(device=dev, priority=hi)
             self._ev_fork = torch.cuda.Event(enable_timing=False)
             self._ev_join = torch.cuda.Event(enable_timing=False)

@@ -5,7 +5,6 @@ import torch
 
 from erasurehead_b200 import Engine, RunConfig, build_scheme, oracle, triple_from_scheme
 from erasurehead_b200.data import generate_gmm, generate_onehot
-from erasurehead_b200.delays import delay_table
 
 pytestmark = pytest.mark.gpu
 

@@ -7,7 +7,7 @@ from scipy.sparse import csr_matrix
 
 from erasurehead_b200 import cli
 from erasurehead_b200.config import parse_argv
-from erasurehead_b200.data import generate_gmm, generate_gmm_to_disk, generate_onehot, load_dataset
+from erasurehead_b200.data import generate_gmm_to_disk, generate_onehot, load_dataset
 from erasurehead_b200.data.dataset import csr_to_ell, ell_to_csr
 from erasurehead_b200.utils import io, metrics
 
