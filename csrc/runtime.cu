@@ -165,6 +165,50 @@ extern "C" int eh_clock_sync_peer(const eh_ws_layout* lay, void* d_ws_local, voi
     return EH_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Bridge to GPUs outside this NVLink domain (another node): their messages and parameters travel
+// as stream-ordered NCCL point-to-point transfers into / out of the same workspace slots, and
+// these two one-thread kernels, enqueued behind the receive, publish what a peer store would have
+// published: the arrival record of a received message (stamped with this GPU's clock) and the
+// parameter flag of a received parameter vector.
+// ------------------------------------------------------------------------------------------
+namespace eh {
+__global__ void bridge_arrival_kernel(uint32_t* flag, uint32_t stamp) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        st_arrival_time(flag);
+        st_release_sys(flag, stamp);
+    }
+}
+__global__ void bridge_beta_flag_kernel(uint32_t* flag, uint32_t stamp) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) st_release_sys(flag, stamp);
+}
+}  // namespace eh
+
+extern "C" void* eh_ws_slot_ptr(const eh_ws_layout* lay, void* d_ws, int worker, int msg, int parity) {
+    if (!lay || !d_ws || worker < 0 || worker >= (int)lay->n_workers || msg < 0 || msg >= (int)lay->n_msgs) return nullptr;
+    return eh::ws_slot(d_ws, *lay, worker, msg, parity & 1);
+}
+extern "C" void* eh_ws_beta_ptr(const eh_ws_layout* lay, void* d_ws, int parity) {
+    if (!lay || !d_ws) return nullptr;
+    return eh::ws_beta(d_ws, *lay, parity & 1);
+}
+extern "C" int eh_bridge_arrival(const eh_ws_layout* lay, void* d_ws, int worker, int msg, uint32_t stamp, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws, "bridge_arrival: null argument");
+    EH_REQUIRE(worker >= 0 && worker < (int)lay->n_workers && msg >= 0 && msg < (int)lay->n_msgs,
+               "bridge_arrival: slot (%d,%d) outside the workspace", worker, msg);
+    bridge_arrival_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ws_flag(d_ws, *lay, worker, msg), stamp);
+    EH_CUDA(cudaGetLastError());
+    return EH_OK;
+}
+extern "C" int eh_bridge_beta_flag(const eh_ws_layout* lay, void* d_ws, uint32_t stamp, void* stream) {
+    using namespace eh;
+    EH_REQUIRE(lay && d_ws, "bridge_beta_flag: null argument");
+    bridge_beta_flag_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ws_beta_flag(d_ws, *lay), stamp);
+    EH_CUDA(cudaGetLastError());
+    return EH_OK;
+}
+
 extern "C" int eh_ws_layout_make(int n_workers, int n_msgs, int d, eh_ws_layout* out) {
     using namespace eh;
     EH_REQUIRE(out, "ws_layout: null out");

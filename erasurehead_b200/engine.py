@@ -189,7 +189,13 @@ class Engine:
         self.ws.sync_clocks()
         # the decoder's SMs: the root's gradient kernels leave them free (no effect on other ranks)
         self.dec_ctas = int(L.eh_decoder_ctas(int(lay.d_pad))) if cfg.decoder == "concurrent" else 0
-        _lib.check(L.eh_set_reserved_sms(self.dec_ctas if ctx.is_root else 0), "eh_set_reserved_sms")
+        # with ranks on other nodes the root also keeps a few SMs free for the NCCL receives of their messages,
+        # so that those do not queue behind the root's own gradient kernels
+        n_remote = len(ctx.remote_ranks)
+        br_sms = min(8, 2 * n_remote) if cfg.decoder == "concurrent" else 0
+        _lib.check(L.eh_set_reserved_sms(self.dec_ctas + br_sms if ctx.is_root else 0), "eh_set_reserved_sms")
+        if n_remote and (cfg.cuda_graph or cfg.beta_push == "multicast"):
+            raise ValueError("ranks on several nodes: --cuda-graph and --beta-push=multicast need one NVLink domain")
         # ---- partitions resident on this GPU (deduplicated across local workers)
         self.parts: Dict[int, tuple] = {}
         mine = ctx.local_workers(spec.n)
@@ -279,6 +285,11 @@ class Engine:
             plan.dec_stream = self._dec_stream.cuda_stream
             plan.ev_fork, plan.ev_join = self._ev_fork.cuda_event, self._ev_join.cuda_event
         self.plan = plan
+        # ---- ranks outside the root's node: NCCL bridge between the workspace blocks (parallel/bridge.py)
+        self.bridge = None
+        if n_remote:
+            from .parallel.bridge import NcclBridge
+            self.bridge = NcclBridge(self)
 
     def _device_partition(self, p: int):
         """(X or ELL idx, y) of partition ``p`` on this GPU (fp32, bf16 when ``--dtype=bf16``, int32 ELL)."""
@@ -363,7 +374,8 @@ class Engine:
                                                                  spec.need_groups, spec.decode)
         D.d, D.d_pad = d, self.ws.lay.d_pad
         D.update_agd = int(cfg.update_rule == "AGD")
-        D.n_peers = self.ctx.world
+        dom = self.ctx.domain_ranks                    # the decoder pushes parameters to the GPUs of its own node
+        D.n_peers = len(dom)
         D.d_group_of = self.t_group.data_ptr()
         D.d_B = self.t_B.data_ptr() if self.t_B is not None else None
         D.d_A = self.t_A.data_ptr() if self.t_A is not None else None
@@ -371,8 +383,8 @@ class Engine:
         D.d_delay_ns, D.d_eta = self.t_delay.data_ptr(), self.t_eta.data_ptr()
         D.d_beta64, D.d_u64 = self.t_beta64.data_ptr(), self.t_u64.data_ptr()
         D.d_ws_local = self.ws.local
-        for r in range(self.ctx.world):
-            D.d_ws_peer[r] = self.ws.peers[r]
+        for i, r in enumerate(dom):
+            D.d_ws_peer[i] = self.ws.peers[r]
         D.d_betaset, D.d_timeset = self.t_betaset.data_ptr(), self.t_timeset.data_ptr()
         D.d_worker_timeset, D.d_weights = self.t_wts.data_ptr(), self.t_weights.data_ptr()
         D.d_ncollected, D.d_tstart = self.t_ncol.data_ptr(), self.t_tstart.data_ptr()
@@ -449,6 +461,8 @@ class Engine:
         if self.dec is not None:
             _lib.check(_lib.lib().eh_decoder_publish(C.byref(self.dec), self.first_round, _lib.stream_ptr()),
                        "eh_decoder_publish")
+        if self.bridge is not None:
+            self.bridge.publish(self.first_round)
         self._cursor = self.first_round
 
     def _poison_slots(self) -> None:
@@ -484,6 +498,13 @@ class Engine:
                        "eh_run_rounds_graph")
             self._graphs.append(exec_)
             torch.cuda.current_stream().wait_stream(self._graph_stream)
+        elif self.bridge is not None:
+            # several nodes: the transfers of a round are enqueued between the rounds' kernels (still no host wait)
+            for it in range(n_rounds):
+                self.bridge.before_round(self._cursor + it)
+                _lib.check(_lib.lib().eh_run_rounds(C.byref(self.plan), self._cursor + it, 1, r0 + it,
+                                                    _lib.stream_ptr()), "eh_run_rounds")
+                self.bridge.after_round(self._cursor + it)
         else:
             _lib.check(_lib.lib().eh_run_rounds(C.byref(self.plan), self._cursor, n_rounds, r0, _lib.stream_ptr()),
                        "eh_run_rounds")
@@ -525,6 +546,8 @@ class Engine:
         return None
 
     def finish(self) -> None:
+        if getattr(self, "bridge", None) is not None:
+            self.bridge.drain()
         self.torch.cuda.synchronize()
         for g in getattr(self, "_graphs", []):
             from .ops import _lib
@@ -780,5 +803,6 @@ class Engine:
     def close(self) -> None:
         if self.on_gpu and getattr(self, "ws", None) is not None:
             self.torch.cuda.synchronize()
+            self.bridge = None                 # its tensors alias the workspace block
             self.ws.close()
             self.ws = None

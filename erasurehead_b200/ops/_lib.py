@@ -146,6 +146,10 @@ def _declare(lib):
         "eh_ws_destroy": (i32, [vp]),
         "eh_ws_reset": (i32, [P(WsLayout), vp, vp]),
         "eh_ws_error": (i32, [P(WsLayout), vp, P(i32), vp]),
+        "eh_ws_slot_ptr": (vp, [P(WsLayout), vp, i32, i32, i32]),
+        "eh_ws_beta_ptr": (vp, [P(WsLayout), vp, i32]),
+        "eh_bridge_arrival": (i32, [P(WsLayout), vp, i32, i32, C.c_uint32, vp]),
+        "eh_bridge_beta_flag": (i32, [P(WsLayout), vp, C.c_uint32, vp]),
         "eh_grad_dense_scratch_bytes": (sz, [i32]),
         "eh_grad_dense": (i32, [P(GradJob), vp, sz, vp]),
         "eh_grad_dense_multi": (i32, [P(GradJob), i32, vp, sz, vp]),

@@ -9,6 +9,9 @@ gradient slots with their arrival flags.  CUDA IPC handles are exchanged once th
   arrival flag (replaces ``comm.Isend([g, MPI.DOUBLE], dest=0, tag=i)``, naive.py:150);
 * the root stores new parameters into *every* GPU's buffer and releases the parameter flag
   (replaces the ``Isend(beta)`` loop, naive.py:97-98).
+
+The mapping covers the GPUs of rank 0's node.  A rank on another node owns an identical block that
+only its own kernels touch; ``parallel/bridge.py`` carries its messages and parameters over NCCL.
 """
 from __future__ import annotations
 
@@ -22,14 +25,6 @@ from .context import DistContext
 class Workspace:
     def __init__(self, ctx: DistContext, n_workers: int, n_msgs: int, d: int):
         self.ctx = ctx
-        if ctx.world > 1:
-            import socket
-            hosts = ctx.all_gather_object(socket.gethostname())
-            if len(set(hosts)) > 1:
-                raise RuntimeError(
-                    "the peer-memory transport (CUDA IPC over NVLink/NVSwitch) needs every rank in one node; "
-                    f"ranks span {sorted(set(hosts))}.  Map the logical workers onto the GPUs of one node "
-                    "(n_procs - 1 workers are spread over the visible GPUs) or run one job per node.")
         L = lib()
         self.lay = WsLayout()
         check(L.eh_ws_layout_make(n_workers, n_msgs, d, C.byref(self.lay)), "eh_ws_layout_make")
@@ -39,11 +34,13 @@ class Workspace:
         self.local = self._local.value
         self._opened: List[int] = []
         handles = ctx.all_gather_object(bytes(handle.raw))
-        # root maps every peer (parameter push); everyone maps the root (gradient ship)
+        # root maps every peer of its node (parameter push); every rank of that node maps the root (gradient
+        # ship).  Ranks on other nodes keep to their own block: their kernels "ship" into the local slots and the
+        # NCCL bridge (parallel/bridge.py) moves messages and parameters between the blocks.
         self.peers: List[int] = [0] * ctx.world
         self.peers[ctx.rank] = self.local
-        if ctx.world > 1:
-            want = range(ctx.world) if ctx.is_root else [0]
+        if ctx.world > 1 and not ctx.is_remote:
+            want = ctx.domain_ranks if ctx.is_root else [0]
             for r in want:
                 if r == ctx.rank:
                     continue
@@ -51,7 +48,7 @@ class Workspace:
                 check(L.eh_ws_open(handles[r], C.byref(p)), f"eh_ws_open(rank {r})")
                 self.peers[r] = p.value
                 self._opened.append(p.value)
-        self.root = self.peers[0]
+        self.root = self.local if ctx.is_remote else self.peers[0]
         self.clock_offset_ns: List[int] = [0] * ctx.world      # peer clock - root clock (root only)
         self.clock_rtt_ns: List[int] = [0] * ctx.world
 
@@ -68,7 +65,7 @@ class Workspace:
         ctx.barrier()
         if ctx.is_root:
             out = torch.zeros(2 * ctx.world, dtype=torch.int64, device=ctx.device)
-            for r in range(1, ctx.world):
+            for r in ctx.domain_ranks[1:]:
                 check(L.eh_clock_sync_root(C.byref(self.lay), self.local, self.peers[r], r << 16, iters,
                                            out.data_ptr() + 8 * r, out.data_ptr() + 8 * (ctx.world + r), stream_ptr()),
                       "eh_clock_sync_root")
@@ -78,7 +75,7 @@ class Workspace:
             self.clock_rtt_ns = [int(x) for x in v[ctx.world:]]
             if any(x < 0 for x in self.clock_rtt_ns[1:]):
                 raise RuntimeError(f"clock alignment with a peer GPU timed out (round trips {self.clock_rtt_ns})")
-        else:
+        elif not ctx.is_remote:
             check(L.eh_clock_sync_peer(C.byref(self.lay), self.local, self.root, ctx.rank << 16, iters, stream_ptr()),
                   "eh_clock_sync_peer")
             torch.cuda.synchronize()

@@ -67,6 +67,16 @@ int eh_ws_open(const unsigned char ipc_handle[64], void** d_ws_peer);
 int eh_ws_close(void* d_ws_peer);
 int eh_ws_destroy(void* d_ws);
 int eh_ws_reset(const eh_ws_layout* lay, void* d_ws, void* stream);
+/* Device addresses inside a workspace block (for transfers issued by the host program). */
+void* eh_ws_slot_ptr(const eh_ws_layout* lay, void* d_ws, int worker, int msg, int parity);   /* float[d_pad] */
+void* eh_ws_beta_ptr(const eh_ws_layout* lay, void* d_ws, int parity);                        /* float[d_pad] */
+/* Bridge to GPUs outside this NVLink domain (other nodes): messages and parameters arrive through
+ * stream-ordered NCCL point-to-point receives into the slots above; these calls, enqueued behind the
+ * receive on the same stream, publish what a peer store would have published -- the arrival record of
+ * (worker, msg) for round stamp-1, stamped with THIS GPU's clock (decoder clock offset of such a worker
+ * is 0), and the parameter flag of the receiving GPU. */
+int eh_bridge_arrival(const eh_ws_layout* lay, void* d_ws, int worker, int msg, uint32_t stamp, void* stream);
+int eh_bridge_beta_flag(const eh_ws_layout* lay, void* d_ws, uint32_t stamp, void* stream);
 /* Read the sticky device error word (0 = none) -- set by any watchdog. */
 int eh_ws_error(const eh_ws_layout* lay, void* d_ws, int* err, void* stream);
 

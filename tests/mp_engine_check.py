@@ -37,9 +37,30 @@ def spaced_delays(rounds, n, seed=0, gap=3e-3):
     return T
 
 
+CURRENT = {"eng": None, "name": ""}
+
+
+def _hang_watch(secs):
+    """EH_DEBUG_HANG=secs: after that long, dump the Python stacks and the flag words of the running engine."""
+    import faulthandler
+    import threading
+    import time
+    faulthandler.dump_traceback_later(secs, exit=False)
+
+    def watch():
+        time.sleep(secs)
+        eng = CURRENT["eng"]
+        br = getattr(eng, "bridge", None)
+        if br is not None:
+            print(f"[hang-watch] scheme={CURRENT['name']} {br.debug_state()}", flush=True)
+    threading.Thread(target=watch, daemon=True).start()
+
+
 def main():
     device = sys.argv[1]
     ctx = init_distributed(device)
+    if os.environ.get("EH_DEBUG_HANG"):
+        _hang_watch(float(os.environ["EH_DEBUG_HANG"]))
     bad = 0
     for name in sys.argv[2:]:
         kw = dict(KW[name])
@@ -65,6 +86,7 @@ def main():
             data = generate_gmm(rows, d, cfg.n_partitions, seed=1)
         dl = spaced_delays(cfg.rounds, n, seed=5)
         eng = Engine(cfg, data, ctx=ctx, delays=dl)
+        CURRENT["eng"], CURRENT["name"] = eng, name
         res = eng.run()
         if ctx.is_root:
             ref = oracle.run_rounds(cfg, build_scheme(cfg, eng.spec.B), data, dl, beta0=eng.beta0, model=eng.model)
@@ -74,6 +96,7 @@ def main():
             print(f"[mp_engine_check] {name}: world={ctx.world} device={ctx.device} rel_err={err:.2e} "
                   f"round_ms={res.timeset.mean() * 1e3:.2f} {'OK' if ok else 'MISMATCH'}", flush=True)
             bad += 0 if ok else 1
+        CURRENT["eng"] = None
         eng.close()
         ctx.barrier()
     if ctx.world > 1:

@@ -63,3 +63,26 @@ def test_two_gpu_multicast_parameter_push():
     rc, out = _torchrun(2, "cuda", ["approx", "coded", "partial_coded"], extra_env={"EH_TEST_BETA_PUSH": "multicast"})
     assert rc == 0, out[-3000:]
     assert out.count("OK") == 3
+
+
+BRIDGED = ["naive", "coded", "replication", "approx", "partial_coded", "partial_replication", "sparse", "softmax",
+           "sparse_softmax"]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(_gpu_count() < 2, reason="needs >= 2 GPUs")
+def test_two_gpu_inter_node_bridge():
+    """EH_NODE_SIZE=1 declares every GPU its own node: rank 1 is reached through the NCCL bridge
+    (parallel/bridge.py) instead of the peer-mapped workspace; iterates and arrival sets must not change."""
+    rc, out = _torchrun(2, "cuda", BRIDGED, extra_env={"EH_NODE_SIZE": "1"})
+    assert rc == 0, out[-3000:]
+    assert out.count("OK") == len(BRIDGED)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(_gpu_count() < 4, reason="needs >= 4 GPUs")
+def test_four_gpu_two_nodes_of_two():
+    """Two GPUs in the root's NVLink domain (peer stores) + two remote GPUs (bridge) in one job."""
+    rc, out = _torchrun(4, "cuda", BRIDGED, extra_env={"EH_NODE_SIZE": "2"})
+    assert rc == 0, out[-3000:]
+    assert out.count("OK") == len(BRIDGED)
