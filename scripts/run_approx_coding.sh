@@ -20,12 +20,15 @@ N_COLS=${N_COLS:-27654}
 # | 1 0 0 cyclic MDS | 1 0 2 ignore stragglers | 1 P 0 partial coded | 1 P 1 partial replication
 MODE=${MODE:-"1 0 3"}
 read IS_CODED PARTS CODED_VER <<< "$MODE"
-HOSTFILE=${HOSTFILE:-}            # optional: one host per line -> one independent single-node job per host (tools/cluster.py torchrun)
+HOSTFILE=${HOSTFILE:-}            # optional: one host per line (the reference's hosts_address, run_approx_coding.sh:47-49)
+ONE_JOB=${ONE_JOB:-1}             # with HOSTFILE: 1 = one job over all hosts, as mpirun --hostfile did (first host's GPUs
+                                  # exchange through peer memory, the others over NCCL); 0 = one independent job per host
 EXTRA="$@"
 
 cd "$(dirname "$0")/.."
 if [ -n "$HOSTFILE" ]; then
-  exec python tools/cluster.py torchrun --hostfile "$HOSTFILE" --gpus-per-node ${N_GPUS} -- \
+  [ "$ONE_JOB" = "1" ] && ONE="--one-job" || ONE=""
+  exec python tools/cluster.py torchrun --hostfile "$HOSTFILE" --gpus-per-node ${N_GPUS} ${ONE} -- \
     main.py ${N_PROCS} ${N_ROWS} ${N_COLS} ${DATA_FOLDER} ${IS_REAL} ${DATASET} ${IS_CODED} ${N_STRAGGLERS} ${PARTS} ${CODED_VER} ${N_COLLECT} ${ADD_DELAY} ${UPDATE_RULE} ${EXTRA}
 fi
 exec python -m torch.distributed.run --nnodes=1 --nproc-per-node ${N_GPUS} --master-addr 127.0.0.1 --master-port ${MASTER_PORT:-29500} \

@@ -104,8 +104,7 @@ def test_spot_launch_requests_waits_and_tags(monkeypatch):
 
 
 def test_torchrun_starts_one_single_node_job_per_host():
-    """All ranks of a process group must share a node (parallel/workspace.py refuses anything else), so the
-    multi-host launcher starts independent single-node jobs; {node} expands per host."""
+    """Default: the multi-host launcher starts independent single-node jobs; {node} expands per host."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import cluster
     c0 = cluster.torchrun_command(0, 2, "/repo", 8, 29500, ["main.py", "9", "--seed={node}", "--output-dir=out{node}of{nodes}"])
@@ -113,3 +112,25 @@ def test_torchrun_starts_one_single_node_job_per_host():
     for c in (c0, c1):
         assert "--nnodes=1 " in c and "--master-addr 127.0.0.1" in c and "--node-rank" not in c
     assert "--seed=0" in c0 and "--output-dir=out0of2" in c0 and "--seed=1" in c1 and "run_node1.log" in c1
+
+
+def test_torchrun_one_job_over_all_hosts():
+    """--one-job: every host joins one rendezvous at the first host; EH_NODE_SIZE declares the node layout."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    c0 = cluster.torchrun_command(0, 3, "/repo", 8, 29500, ["main.py", "25"], master="10.0.0.1")
+    c2 = cluster.torchrun_command(2, 3, "/repo", 8, 29500, ["main.py", "25"], master="10.0.0.1")
+    for i, c in ((0, c0), (2, c2)):
+        assert f"--nnodes=3 --node-rank={i} " in c and "--master-addr 10.0.0.1" in c and "EH_NODE_SIZE=8 " in c
+    seen = []
+    cluster_fan_out, cluster.fan_out = cluster.fan_out, lambda hosts, f: seen.extend(f(h) for h in hosts)
+    try:
+        hf = os.path.join(os.path.dirname(__file__), "_hosts_tmp")
+        with open(hf, "w") as f:
+            f.write("10.0.0.1\n10.0.0.2\n")
+        cluster.main(["torchrun", "--hostfile", hf, "--gpus-per-node", "4", "--one-job", "--", "main.py", "9"])
+    finally:
+        cluster.fan_out = cluster_fan_out
+        os.remove(hf)
+    assert len(seen) == 2 and all("--nnodes=2" in c and "--master-addr 10.0.0.1" in c for c in seen)
+    assert "--node-rank=1" in seen[1] and "EH_NODE_SIZE=4" in seen[1]

@@ -23,11 +23,13 @@ sense for GPU nodes:
   clean_launch_and_run --count N -- main.py <13 positionals>
                                                shutdown, launch, wait until every instance is up and reachable,
                                                get_hosts, bootstrap, install, torchrun (pytorch_ec2.py:938 map entry)
-  torchrun --hostfile F --gpus-per-node G -- main.py <13 positionals>
-                                               one INDEPENDENT single-node ``torch.distributed.run`` job per host (the
-                                               NVLink peer-memory transport lives inside one node,
-                                               parallel/workspace.py); ``{node}`` / ``{nodes}`` in the arguments expand
-                                               to the host's index / the host count (seeds, output directories)
+  torchrun --hostfile F --gpus-per-node G [--one-job] -- main.py <13 positionals>
+                                               default: one INDEPENDENT single-node ``torch.distributed.run`` job per
+                                               host; ``{node}`` / ``{nodes}`` in the arguments expand to the host's
+                                               index / the host count (seeds, output directories).
+                                               --one-job: ONE job over all hosts, as ``mpirun --hostfile`` ran the
+                                               reference: the first host's GPUs form the peer-memory domain, the
+                                               other hosts' GPUs are reached over NCCL (parallel/bridge.py)
 
 Unlike the reference, processes are never killed by pattern (``pkill python``): the launcher
 records the PID it started on every host under ``~/.erasurehead_b200/pids`` and only those are
@@ -291,20 +293,33 @@ def cmd_clean_launch_and_run(a):
     cmd_torchrun(a)
 
 
-def torchrun_command(host_index: int, n_hosts: int, repo: str, gpus_per_node: int, port: int, rest: List[str]) -> str:
-    """Shell command for ONE host: an independent single-node job (all ranks of a process group must share
-    a node, parallel/workspace.py).  `{node}` and `{nodes}` in the arguments become the host's index and the
-    host count, so that hosts can run different seeds / configurations / output directories."""
+def torchrun_command(host_index: int, n_hosts: int, repo: str, gpus_per_node: int, port: int, rest: List[str],
+                     master: str = "") -> str:
+    """Shell command for ONE host.
+
+    Default (``master`` empty): an independent single-node job per host.  ``{node}`` and ``{nodes}`` in the
+    arguments become the host's index and the host count, so that hosts can run different seeds /
+    configurations / output directories.
+    With ``master`` (the first host's address): this host's share of ONE job over all hosts -- what
+    ``mpirun --hostfile`` did for the reference (run_approx_coding.sh:47-49).  Rank 0's node is the
+    peer-memory domain, the GPUs of the other hosts are reached through the NCCL bridge
+    (erasurehead_b200/parallel/bridge.py); EH_NODE_SIZE tells every rank the layout without a collective."""
     args = " ".join(shlex.quote(x.replace("{node}", str(host_index)).replace("{nodes}", str(n_hosts))) for x in rest)
-    return (f"mkdir -p {PID_DIR} && cd {repo} && setsid python -m torch.distributed.run --nnodes=1 "
-            f"--nproc-per-node={gpus_per_node} --master-addr 127.0.0.1 --master-port {port} {args} "
+    if master:
+        rdzv = (f"EH_NODE_SIZE={gpus_per_node} python -m torch.distributed.run --nnodes={n_hosts} --node-rank={host_index} "
+                f"--nproc-per-node={gpus_per_node} --master-addr {master} --master-port {port}")
+    else:
+        rdzv = (f"python -m torch.distributed.run --nnodes=1 --nproc-per-node={gpus_per_node} "
+                f"--master-addr 127.0.0.1 --master-port {port}")
+    return (f"mkdir -p {PID_DIR} && cd {repo} && setsid {rdzv} {args} "
             f"> run_node{host_index}.log 2>&1 & echo $! > {PID_DIR}/run.pid; wait; tail -5 run_node{host_index}.log")
 
 
 def cmd_torchrun(a):
     hosts = read_hosts(a.hostfile)
     repo = a.repo or os.getcwd()
-    fan_out(hosts, lambda h: torchrun_command(hosts.index(h), len(hosts), repo, a.gpus_per_node, a.port, a.rest))
+    master = hosts[0] if getattr(a, "one_job", False) and len(hosts) > 1 else ""
+    fan_out(hosts, lambda h: torchrun_command(hosts.index(h), len(hosts), repo, a.gpus_per_node, a.port, a.rest, master))
 
 
 def main(argv=None):
@@ -324,6 +339,7 @@ def main(argv=None):
     p = sub.add_parser("setup_nfs"); p.add_argument("hostfile"); p.add_argument("export_dir"); p.set_defaults(fn=cmd_setup_nfs)
     p = sub.add_parser("torchrun"); p.add_argument("--hostfile", required=True)
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
+    p.add_argument("--one-job", action="store_true", help="one job over all hosts instead of one job per host")
     p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_torchrun)
     p = sub.add_parser("clean_launch_and_run"); p.add_argument("--count", type=int, default=cfg["n_workers"])
     p.add_argument("--method", choices=["spot", "ondemand", "reserved"]); p.add_argument("--spot-price")
