@@ -49,16 +49,17 @@ def messages_of(spec, ctx, rank: int) -> List[Tuple[int, int]]:
     return out
 
 
-_PAIR_GROUPS: Dict[int, object] = {}      # remote rank -> process group {0, rank}; created once per process
+_PAIR_GROUPS: Dict[Tuple[int, int], object] = {}      # (world group, remote rank) -> process group {0, rank}
 
 
 def pair_group(x: int):
     """The two-rank group of rank 0 and remote rank ``x``.  Creation is collective over the whole job, so every
     rank calls this for every remote rank in the same order (the engines of a job are built in lock-step)."""
     import torch.distributed as dist
-    if x not in _PAIR_GROUPS:
-        _PAIR_GROUPS[x] = dist.new_group(ranks=[0, x])
-    return _PAIR_GROUPS[x]
+    key = (id(dist.group.WORLD), x)                     # a re-initialised process group gets new pair groups
+    if key not in _PAIR_GROUPS:
+        _PAIR_GROUPS[key] = dist.new_group(ranks=[0, x])
+    return _PAIR_GROUPS[key]
 
 
 class NcclBridge:
