@@ -12,6 +12,11 @@ division" the files were written for.  Nothing else is touched: same drivers, sa
 / sklearn calls, same file formats, same timers.
 
     python baseline/py2run.py main.py <13 positionals>          (cwd = baseline/_ref)
+
+``EH_NP_SEED=<int>`` seeds numpy's global generator before the script starts.  The reference draws its
+initial parameters (naive / replication / approximate) and its code matrix B from that generator without
+seeding it; with the variable set the run is reproducible, which is what the parity tests compare against.
+The benchmark arm leaves it unset.
 """
 import ast
 import builtins
@@ -95,6 +100,8 @@ def main():
     sys.meta_path.insert(0, _Finder([os.path.join(root, "src"), root]))
     sys.argv = [sys.argv[1]] + sys.argv[2:]
     sys.path.insert(0, root)
+    if os.environ.get("EH_NP_SEED"):
+        np.random.seed(int(os.environ["EH_NP_SEED"]))
     with open(script, "rb") as f:
         code = compile_py2(f.read(), script)
     g = {"__name__": "__main__", "__file__": script, "__builtins__": builtins}
