@@ -29,7 +29,7 @@ POSITIONALS = (
 
 USAGE = ("Usage: python main.py " + " ".join(POSITIONALS) +
          " [--rounds=R --alpha=A --eta0=E --lr-schedule=const|t0decay|expdecay --seed=S "
-         "--delay-scale=SEC --delay-mode=exp|fixed|dead|none --gpus=N --synthetic "
+         "--delay-scale=SEC --delay-mode=exp|fixed|dead|none --delay-carryover --gpus=N --synthetic "
          "--model=logistic|linear|softmax --classes=C --compat --output-dir=DIR "
          "--checkpoint-every=K --resume=PATH --eval=full|none --metrics-jsonl=PATH "
          "--synthetic-nnz=K --init=scheme|zeros|randn --dtype=fp32|bf16 --decoder=concurrent|inline --abandon "
@@ -91,6 +91,10 @@ class RunConfig:
     delay_scale: float = 0.5               # mean of the exponential delay in seconds (naive.py:147)
     delay_mode: str = "exp"                # exp | fixed | dead | none
     delay_fixed: float = 0.5               # sleep for the fixed-straggler-set variant (naive.py:143-145)
+    delay_carryover: Optional[bool] = None  # a worker still inside its delay when a round ends starts the next round
+                                           # late by what is left (what the reference's coded driver does: its master
+                                           # never waits for stragglers, coded.py:137-166, so a sleeping worker stays
+                                           # busy).  None = only with --compat for the coded scheme
     gpus: int = 0                          # 0 = all visible
     synthetic: bool = False                # generate data on the GPU instead of reading input_dir
     synthetic_nnz: int = 0                 # --synthetic with is_real=1: ones per row (0 = the named dataset's, data/shapes.py)
@@ -133,6 +137,8 @@ class RunConfig:
             # Q9: these drivers hard-wire AGD and have no delay block.
             self.update_rule = "AGD"
             self.add_delay = 0
+        if self.delay_carryover is None:
+            self.delay_carryover = bool(self.compat and self.scheme == "coded")
 
     # ---- derived ----
     @property

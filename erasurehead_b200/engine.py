@@ -135,6 +135,9 @@ class Engine:
             cfg.rounds - self.first_round, self.spec.n, mode=cfg.delay_mode, scale=cfg.delay_scale,
             n_stragglers=cfg.n_stragglers, fixed_sleep=cfg.delay_fixed, enabled=bool(cfg.add_delay),
             first_round=self.first_round)
+        if cfg.delay_carryover and cfg.add_delay:
+            # backlog of workers that were still inside their delay when a round ended (starts empty on a resume)
+            self.delays = oracle.carryover_delays(self.spec, self.delays)
         self.result: Optional[oracle.RunResult] = None
         self.launches = 0
         # multi-column models (softmax): parameters travel as one flat class-major vector

@@ -81,6 +81,27 @@ def worker_messages(model: Model, spec: SchemeSpec, data, w: int, beta: np.ndarr
     return out
 
 
+def carryover_delays(spec: SchemeSpec, delays: np.ndarray) -> np.ndarray:
+    """Delay table of a run whose master never waits for stragglers between rounds.
+
+    In the reference's coded driver (coded.py:137-166) the master moves on as soon as n - s messages are in,
+    while a straggler is still inside its ``time.sleep``: that worker picks up the next parameters only when it
+    wakes, so its next message arrives late by what was left of the old delay, on top of the new one (its
+    replication / approximate drivers ``Waitall`` on every straggler after each round, replication.py:179-180,
+    so there every round starts fresh -- SURVEY Q5).  This replays that backlog from the delay table and the
+    stop rule alone:  ``eff[i] = backlog + delays[i]``,  ``backlog = max(0, eff[i] - t_stop[i])``,  and returns the
+    effective table, which the oracle and the device decoder then consume like any other.  The compute and
+    transport time of a round (milliseconds against delays of half a second) is not part of the replay."""
+    delays = np.asarray(delays, dtype=np.float64)
+    eff = np.empty_like(delays)
+    backlog = np.zeros(delays.shape[1])
+    for i in range(delays.shape[0]):
+        eff[i] = backlog + delays[i]
+        t_stop = plan_round(spec, eff[i], round_index=i)[2]
+        backlog = np.where(np.isfinite(eff[i]), np.maximum(0.0, eff[i] - t_stop), np.inf)
+    return eff
+
+
 def plan_round(spec: SchemeSpec, delay_row: np.ndarray, compute_time: float = 0.0, round_index: int = 0):
     """Replay the master's Waitany loop for one round given only the message delays.
 

@@ -158,3 +158,35 @@ def test_gradient_encoding_folds_into_residual():
     assert np.allclose(m.gradient(X, y, np.full(20, c), b), want)
     ml = get_model("linear")
     assert np.allclose(ml.gradient(X, y, np.ones(20), b), -2 * X.T.dot(y - X.dot(b)))      # naive.py:345-346
+
+
+def test_carryover_delays_replay_a_backlog():
+    """A worker still inside its delay when the round ends starts the next round late by what is left
+    (the reference's coded driver: its master never waits for stragglers, coded.py:137-166)."""
+    from erasurehead_b200 import RunConfig, build_scheme, oracle, triple_from_scheme
+    ic, pp, cv = triple_from_scheme("coded", 0)
+    spec = build_scheme(RunConfig(4, 3 * 40, 6, "", 0, "x", ic, 1, pp, cv, 0, 1, "AGD", seed=1))      # 3 workers, waits for 2
+    dl = np.array([[0.1, 0.2, 1.0],
+                   [0.5, 0.5, 0.1],
+                   [0.3, 0.05, 0.05]])
+    eff = oracle.carryover_delays(spec, dl)
+    assert np.allclose(eff[0], [0.1, 0.2, 1.0])                 # round 0 ends at 0.2, worker 2 has 0.8 s left
+    assert np.allclose(eff[1], [0.5, 0.5, 0.9])                 # ... ends at 0.5, worker 2 has 0.4 s left
+    assert np.allclose(eff[2], [0.3, 0.05, 0.45])
+    # a scheme that waits for everybody never builds a backlog
+    ic, pp, cv = triple_from_scheme("naive", 0)
+    naive = build_scheme(RunConfig(4, 3 * 40, 6, "", 0, "x", ic, 0, pp, cv, 0, 1, "AGD", seed=1))
+    assert np.allclose(oracle.carryover_delays(naive, dl), dl)
+    # a dead worker stays dead
+    dl[0, 2] = np.inf
+    assert np.isinf(oracle.carryover_delays(spec, dl)[:, 2]).all()
+
+
+def test_carryover_is_on_only_for_compat_coded():
+    from erasurehead_b200 import RunConfig, triple_from_scheme
+    mk = lambda scheme, **kw: RunConfig(5, 480, 6, "", 0, "x", *triple_from_scheme(scheme, 0)[:1], 1,
+                                        *triple_from_scheme(scheme, 0)[1:], 0, 1, "AGD", **kw)
+    assert mk("coded", compat=True).delay_carryover is True
+    assert mk("coded").delay_carryover is False
+    assert mk("replication", compat=True).delay_carryover is False
+    assert mk("replication", delay_carryover=True).delay_carryover is True
