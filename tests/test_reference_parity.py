@@ -183,3 +183,29 @@ def test_injected_delays_collect_the_same_workers_as_the_reference(tmp_path, nam
         assert np.abs(tl - ref_train).max() <= 1.5e-3
         # arrival times: the reference measures sleep + compute + transport, the model only the sleep
         assert np.abs(wt[both] - ref_wt[both]).max() < 0.05
+
+
+@pytest.mark.parametrize("partial", [0, 1])
+def test_files_written_by_the_reference_generator_are_read_here(tmp_path, partial):
+    """The other direction of the file contract: generate_data.py of the reference (run unmodified, Python-2
+    division supplied at import) writes the partitions, this framework's reader and CLI consume them."""
+    from erasurehead_b200.data import load_dataset
+    n_procs, rows, cols, s, P = 5, 8 * 60, 10, 1, 3
+    ref_src = os.path.join(ROOT, "baseline", "_ref", "src")
+    if not os.path.exists(os.path.join(ref_src, "generate_data.py")):
+        subprocess.check_call(["bash", os.path.join(ROOT, "baseline", "install_ref.sh")], stdout=subprocess.DEVNULL)
+    cmd = [sys.executable, os.path.join(ROOT, "baseline", "py2run.py"), os.path.join(ref_src, "generate_data.py"),
+           str(n_procs), str(rows), str(cols), str(tmp_path), str(s), str(P), str(partial)]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ref_src, env=dict(os.environ, EH_NP_SEED="11"))
+    assert p.returncode == 0 and "Done with Test data" in p.stdout, (p.stdout + p.stderr)[-2000:]
+    triple = ("1", str(P), "1") if partial else ("1", "0", "1")
+    args = [str(n_procs), str(rows), str(cols), str(tmp_path) + "/", "0", "x", triple[0], str(s), triple[1], triple[2],
+            "0", "0", "AGD"]
+    cfg = parse_argv(args + ["--gpus=-1", "--quiet", "--seed=1", "--rounds=30", "--init=zeros", "--eta0=0.5"])
+    data = load_dataset(cfg.data_dir, cfg.n_partitions, False, cols)
+    n_parts = (n_procs - 1) * (P - s) if partial else n_procs - 1
+    assert cfg.n_partitions == n_parts and len(data.parts) == n_parts
+    assert data.rows_per_part == rows // n_parts and data.n_cols == cols
+    assert set(np.unique(data.y)) <= {-1.0, 1.0} and data.X_test.shape == (int(0.2 * rows), cols)
+    ev = cli.run(cfg)["evaluation"]
+    assert ev.training_loss[-1] < ev.training_loss[0] and ev.auc[-1] > 0.6
