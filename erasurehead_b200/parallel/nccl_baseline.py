@@ -39,6 +39,8 @@ class NcclBaselineEngine:
         self.delays = delays if delays is not None else delay_table(
             cfg.rounds, n, mode=cfg.delay_mode, scale=cfg.delay_scale, n_stragglers=cfg.n_stragglers,
             enabled=bool(cfg.add_delay))
+        if cfg.delay_carryover and cfg.add_delay:
+            self.delays = oracle.carryover_delays(spec, self.delays)
         self.mine = self.ctx.local_workers(n)
         self.parts = {}
         for p in sorted({sg.partition for w in self.mine for sg in spec.segments[w]}):
