@@ -134,3 +134,28 @@ def test_torchrun_one_job_over_all_hosts():
         os.remove(hf)
     assert len(seen) == 2 and all("--nnodes=2" in c and "--master-addr 10.0.0.1" in c for c in seen)
     assert "--node-rank=1" in seen[1] and "EH_NODE_SIZE=4" in seen[1]
+
+
+def test_grid_search_deals_points_to_hosts():
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    pts = cluster.grid_points(["eta0=1,10", "num_collect=4,6,8"])
+    assert len(pts) == 6 and pts[0] == {"eta0": "1", "num_collect": "4"} and pts[-1] == {"eta0": "10", "num_collect": "8"}
+    rest = ["main.py", "9", "7680", "128", "/d/", "0", "x", "1", "1", "0", "3", "{num_collect}", "1", "AGD", "--eta0={eta0}"]
+    cmds = cluster.grid_commands(4, "/repo", 8, 29500, rest, pts, "/shared/grid_search")
+    assert len(cmds) == 4
+    assert cmds[0].count("torch.distributed.run") == 2 and cmds[3].count("torch.distributed.run") == 1      # 6 points over 4 hosts
+    assert "--eta0=1 " in cmds[0] and " 3 4 1 AGD" in cmds[0] and "/shared/grid_search/eta0_1_num_collect_4/" in cmds[0]
+    assert "--output-dir=/shared/grid_search/eta0_10_num_collect_4/" in cmds[3]
+    assert "{" not in "".join(cmds)
+    seen = []
+    keep, cluster.fan_out = cluster.fan_out, lambda hosts, f: seen.extend(f(h) for h in hosts)
+    hf = os.path.join(os.path.dirname(__file__), "_hosts_tmp2")
+    try:
+        with open(hf, "w") as f:
+            f.write("a\nb\n")
+        cluster.main(["grid_search", "--hostfile", hf, "--grid", "seed=1,2,3", "--out-dir", "/o", "--", "main.py", "9", "--seed={seed}"])
+    finally:
+        cluster.fan_out = keep
+        os.remove(hf)
+    assert len(seen) == 2 and "--seed=1" in seen[0] and "--seed=3" in seen[0] and "--seed=2" in seen[1]

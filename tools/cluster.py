@@ -31,6 +31,12 @@ sense for GPU nodes:
                                                reference: the first host's GPUs form the peer-memory domain, the
                                                other hosts' GPUs are reached over NCCL (parallel/bridge.py)
 
+  grid_search --hostfile F --grid name=v1,v2 [--grid ...] --out-dir D -- main.py <13 positionals> --opt={name}
+                                               hyper-parameter grid dealt round-robin to the hosts, each host runs its
+                                               points one after the other and writes results + log under D/<point>/
+                                               (role of run_mxnet_grid_search / run_mxnet_loss_curve, :374-652: the
+                                               per-iteration loss curves are the result files of every run)
+
 Unlike the reference, processes are never killed by pattern (``pkill python``): the launcher
 records the PID it started on every host under ``~/.erasurehead_b200/pids`` and only those are
 signalled.  Credentials come from the SSH agent / ``~/.ssh/config``; nothing is hard-coded.
@@ -322,6 +328,53 @@ def cmd_torchrun(a):
     fan_out(hosts, lambda h: torchrun_command(hosts.index(h), len(hosts), repo, a.gpus_per_node, a.port, a.rest, master))
 
 
+def grid_points(specs: List[str]) -> List[dict]:
+    """``["eta0=1,10", "n_collect=4,6"]`` -> the Cartesian product as a list of {name: value} dicts."""
+    import itertools
+    names, values = [], []
+    for sp in specs:
+        name, _, vals = sp.partition("=")
+        if not name or not vals:
+            raise SystemExit(f"--grid wants name=v1,v2,... (got {sp!r})")
+        names.append(name)
+        values.append(vals.split(","))
+    return [dict(zip(names, combo)) for combo in itertools.product(*values)]
+
+
+def grid_commands(n_hosts: int, repo: str, gpus_per_node: int, port: int, rest: List[str], points: List[dict],
+                  out_dir: str) -> List[str]:
+    """One shell command per host: the grid points are dealt round-robin to the hosts and every host runs its
+    share one after the other as single-node jobs (the role of the reference tool's ``run_mxnet_grid_search`` /
+    ``run_mxnet_loss_curve``, pytorch_ec2.py:374-652: host k works on slice k of the grid and writes under the
+    shared directory).  ``{name}`` in the arguments is replaced by the point's value; the result files of a point
+    go to ``<out_dir>/<name>_<value>_...`` (``--output-dir``), its log next to them."""
+    cmds = []
+    for h in range(n_hosts):
+        runs = []
+        for pt in points[h::n_hosts]:
+            tag = "_".join(f"{k}_{v}" for k, v in pt.items())
+            args = [x for x in rest]
+            for k, v in pt.items():
+                args = [a.replace("{" + k + "}", v) for a in args]
+            d = f"{out_dir.rstrip('/')}/{tag}"
+            argstr = " ".join(shlex.quote(a) for a in args + [f"--output-dir={d}/"])
+            runs.append(f"mkdir -p {shlex.quote(d)} && python -m torch.distributed.run --nnodes=1 "
+                        f"--nproc-per-node={gpus_per_node} --master-addr 127.0.0.1 --master-port {port} {argstr} "
+                        f"> {shlex.quote(d)}/run.log 2>&1")
+        body = " ; ".join(runs) if runs else "true"
+        cmds.append(f"mkdir -p {PID_DIR} && cd {repo} && (setsid bash -c {shlex.quote(body)} & echo $! > {PID_DIR}/run.pid; wait)")
+    return cmds
+
+
+def cmd_grid_search(a):
+    hosts = read_hosts(a.hostfile)
+    repo = a.repo or os.getcwd()
+    points = grid_points(a.grid)
+    cmds = grid_commands(len(hosts), repo, a.gpus_per_node, a.port, a.rest, points, a.out_dir or cfg["nfs_mount_point"] + "/grid_search")
+    print(f"{len(points)} grid points over {len(hosts)} hosts")
+    fan_out(hosts, lambda h: cmds[hosts.index(h)])
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     sub = ap.add_subparsers(dest="cmd", required=True)
@@ -341,6 +394,11 @@ def main(argv=None):
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
     p.add_argument("--one-job", action="store_true", help="one job over all hosts instead of one job per host")
     p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_torchrun)
+    p = sub.add_parser("grid_search"); p.add_argument("--hostfile", required=True)
+    p.add_argument("--grid", action="append", default=[], help="name=v1,v2,... (repeatable); {name} in the arguments")
+    p.add_argument("--out-dir", default=""); p.add_argument("--gpus-per-node", type=int, default=8)
+    p.add_argument("--port", type=int, default=29500); p.add_argument("--repo")
+    p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_grid_search)
     p = sub.add_parser("clean_launch_and_run"); p.add_argument("--count", type=int, default=cfg["n_workers"])
     p.add_argument("--method", choices=["spot", "ondemand", "reserved"]); p.add_argument("--spot-price")
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
