@@ -87,6 +87,7 @@ class RunConfig:
     lr_schedule: str = "const"             # const | t0decay (main.py:41-43) | expdecay (main.py:46)
     lr_t0: float = 90.0
     lr_decay: float = 0.98
+    lr_values: Optional[Sequence[float]] = None   # explicit step per round (the reference's params[2]); overrides the schedule
     seed: Optional[int] = 0
     delay_scale: float = 0.5               # mean of the exponential delay in seconds (naive.py:147)
     delay_mode: str = "exp"                # exp | fixed | dead | none
@@ -179,6 +180,11 @@ class RunConfig:
     def learning_rates(self) -> np.ndarray:
         """The three schedules present (two of them commented out) in ``main.py:37-46``."""
         R = self.rounds
+        if self.lr_values is not None:
+            v = np.asarray(self.lr_values, dtype=np.float64).reshape(-1)
+            if v.size < R:
+                raise ValueError(f"lr_values has {v.size} entries for {R} rounds")
+            return v[:R].copy()
         if self.lr_schedule == "const":
             return self.eta0 * np.ones(R)
         if self.lr_schedule == "t0decay":
