@@ -149,17 +149,18 @@ def test_linear_regression_path_matches_the_reference_output(tmp_path):
 
 
 @pytest.mark.skipif(not os.environ.get("EH_SLOW_TESTS"), reason="two minutes of real Exp(0.5 s) sleeps each; set EH_SLOW_TESTS=1")
-@pytest.mark.parametrize("name,coded_ver,k,prefix", [
-    ("approx", "3", 2, "replication_acc_1"),          # Q2: AGC writes replication's file names
-    ("coded", "0", 0, "coded_acc_1"),
-    ("replication", "1", 0, "replication_acc_1"),
+@pytest.mark.parametrize("name,coded_ver,k,prefix,n_procs", [
+    ("approx", "3", 2, "replication_acc_1", 5),       # Q2: AGC writes replication's file names
+    ("coded", "0", 0, "coded_acc_1", 5),
+    ("replication", "1", 0, "replication_acc_1", 5),
+    ("approx3groups", "3", 2, "replication_acc_1", 7),    # 3 groups of 2, stop after 2 arrivals: duplicates inside a group
 ])
-def test_injected_delays_collect_the_same_workers_as_the_reference(tmp_path, name, coded_ver, k, prefix):
+def test_injected_delays_collect_the_same_workers_as_the_reference(tmp_path, name, coded_ver, k, prefix, n_procs):
     """The reference's own straggler model switched on: the seeded Exp(0.5 s) table (approximate_coding.py:198-207,
     coded.py, replication.py alike) decides who arrives first, so the set of workers the master collects in each
     round, and from it every iterate, must be the same on both sides (up to two delays closer than the
     reference's compute jitter).  The recorded outcome is in profiles/reference_parity_delays.txt."""
-    n_procs, rows, cols, s = 5, 8 * 60, 10, 1
+    rows, cols, s = 8 * 60, 10, 1
     out = generate_gmm_to_disk(n_procs, rows, cols, str(tmp_path), s, 0, 0, seed=3)
     args = [str(n_procs), str(rows), str(cols), str(tmp_path) + "/", "0", "x", "1", str(s), "0", coded_ver, str(k), "1", "AGD"]
     txt = run_reference(args, np_seed=NP_SEED, timeout=900)
