@@ -45,6 +45,8 @@ def run(cfg: RunConfig, data=None, ctx=None, out=None) -> Optional[dict]:
                             dtype=np.float32 if on_gpu else float)
     eng = Engine(cfg, data, ctx=ctx)
     say = (lambda *a: print(*a, file=out)) if ctx.is_root and not cfg.quiet else (lambda *a: None)
+    if ctx.remote_ranks:
+        say(f"ranks {ctx.domain_ranks} share rank 0's node (peer memory); ranks {ctx.remote_ranks} are reached over NCCL")
     say(BANNERS[cfg.scheme].format(s=cfg.n_stragglers, delay=cfg.add_delay))
     if cfg.scheme.startswith("partial_"):
         say("Stragglers are allowed to be atmost %.2f times slower"

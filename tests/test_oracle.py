@@ -190,3 +190,34 @@ def test_carryover_is_on_only_for_compat_coded():
     assert mk("coded").delay_carryover is False
     assert mk("replication", compat=True).delay_carryover is False
     assert mk("replication", delay_carryover=True).delay_carryover is True
+
+
+def test_carryover_properties():
+    """Over random tables: a backlog only ever adds delay, never for a scheme that waits for every worker, and a
+    round's effective delay is the raw one exactly for the workers that were collected in the round before."""
+    from hypothesis import given, settings, strategies as st
+    from erasurehead_b200 import RunConfig, build_scheme, oracle, triple_from_scheme
+
+    def spec_of(scheme, n, s, k=0):
+        ic, pp, cv = triple_from_scheme(scheme, 0)
+        return build_scheme(RunConfig(n + 1, n * 16, 4, "", 0, "x", ic, s, pp, cv, k, 1, "AGD", seed=1))
+
+    specs = [spec_of("coded", 6, 2), spec_of("approx", 6, 1, 3), spec_of("avoidstragg", 6, 2), spec_of("replication", 6, 2)]
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.integers(0, 2 ** 31 - 1), st.integers(0, 3))
+    def check(seed, which):
+        spec = specs[which]
+        dl = np.random.RandomState(seed).exponential(0.5, (12, 6))
+        eff = oracle.carryover_delays(spec, dl)
+        assert (eff >= dl - 1e-12).all()
+        for i in range(1, 12):
+            wt = oracle.plan_round(spec, eff[i - 1])[4]
+            t_stop = oracle.plan_round(spec, eff[i - 1])[2]
+            on_time = eff[i - 1] <= t_stop + 1e-12
+            assert np.allclose(eff[i][on_time], dl[i][on_time])
+            assert (wt[~on_time] < 0).all()                    # whoever was still busy had not been collected
+    check()
+    naive = spec_of("naive", 6, 0)
+    dl = np.random.RandomState(0).exponential(0.5, (12, 6))
+    assert np.allclose(oracle.carryover_delays(naive, dl), dl)
