@@ -25,6 +25,8 @@ test:
 	$(PY) -m pytest tests -q -m "not gpu"
 test-gpu:
 	$(PY) -m pytest tests -q -m gpu
+test-parity-delays:      # the unmodified reference with its real Exp(0.5 s) sleeps against the model (CPU, ~2 min per scheme)
+	EH_SLOW_TESTS=1 $(PY) -m pytest tests/test_reference_parity.py -q -s -k injected_delays
 generate_random_data:
 	$(PY) -m erasurehead_b200.data.generate $(N_PROCS) $(N_ROWS) $(N_COLS) $(DATA_FOLDER) $(N_STRAGGLERS) $(N_PARTITIONS) $(PARTIAL_CODED)
 arrange_real_data:
@@ -47,4 +49,4 @@ sanitize:
 	bash tools/sanitize.sh
 bench:
 	$(PY) bench.py
-.PHONY: build test test-gpu generate_random_data arrange_real_data naive cyccoded repcoded avoidstragg approx partialrepcoded partialcyccoded sanitize bench
+.PHONY: build test test-gpu test-parity-delays generate_random_data arrange_real_data naive cyccoded repcoded avoidstragg approx partialrepcoded partialcyccoded sanitize bench
