@@ -138,6 +138,8 @@ class RunConfig:
             # Q9: these drivers hard-wire AGD and have no delay block.
             self.update_rule = "AGD"
             self.add_delay = 0
+        if self.resume is True or self.resume == "":
+            raise ValueError("--resume needs the path of a checkpoint file (--resume=PATH)")
         if self.delay_carryover is None:
             self.delay_carryover = bool(self.compat and self.scheme == "coded")
 

@@ -576,6 +576,15 @@ class Engine:
                 res = oracle.run_rounds(cfg, self.spec, self.data, self.delays[:R], beta0=self.beta0, u0=self.u0,
                                         first_round=self.first_round, rounds=R, model=self.model)
                 res.wall_time = time.time() - t0
+                if cfg.checkpoint_every > 0 and R > 0:
+                    # same file at the same cadence as the device path: the state after the last full chunk
+                    k = R if R % cfg.checkpoint_every == 0 else R - R % cfg.checkpoint_every
+                    if k > 0:
+                        self.result = res if k == R else oracle.RunResult(
+                            betaset=res.betaset[:k], timeset=res.timeset[:k], worker_timeset=res.worker_timeset[:k],
+                            weights=res.weights[:k], n_collected=res.n_collected[:k],
+                            u=self._u_after(res, k), beta=res.betaset[k - 1])
+                        self.save_checkpoint(self._ckpt_path(), self.first_round + k)
             self.result = res
             self.ctx.barrier()
             return res
@@ -597,6 +606,16 @@ class Engine:
             res.wall_time = time.time() - t0
         self.result = res
         return res
+
+    def _u_after(self, res: oracle.RunResult, k: int) -> np.ndarray:
+        """AGD momentum state after ``k`` rounds of ``res`` (recomputed from the stored iterates:
+        ``u_{i+1} = beta_i + (beta_{i+1} - beta_i) / theta_i``, naive.py:119-123)."""
+        if self.cfg.update_rule != "AGD" or k >= len(res.betaset):
+            return res.u
+        i = self.first_round + k - 1
+        prev = res.betaset[k - 2] if k >= 2 else self.beta0
+        theta = 2.0 / (i + 2.0)
+        return prev + (res.betaset[k - 1] - prev) * (1.0 / theta)
 
     def _collect(self, R: int) -> oracle.RunResult:
         cpu = lambda t: t[:R].detach().cpu().numpy()

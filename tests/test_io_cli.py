@@ -216,3 +216,19 @@ def test_lazy_dataset_reads_partitions_on_demand(tmp_path):
     generate_onehot(4 * 200, 500, 9, 4, seed=1).save(str(tmp_path / "oh") + "/")
     c = load_dataset(str(tmp_path / "oh") + "/", 4, True, 500, lazy=True)
     assert c.is_sparse and c.ell(3).shape == (200, 9) and c.labels(3).shape == (200,)
+
+
+def test_cli_checkpoint_every_writes_a_resumable_file_on_cpu(tmp_path):
+    """--checkpoint-every on the CPU path: the file holds the state after the last full chunk (7 rounds, every 3
+    -> after round 6), and a run resumed from it reproduces the remaining iterates of an uninterrupted run."""
+    generate_gmm_to_disk(9, 800, 6, str(tmp_path), 1, 0, 0, seed=1)
+    base = f"9 800 6 {tmp_path} 0 x 1 1 0 3 5 1 AGD --gpus=-1 --quiet"
+    full = cli.run(parse_argv((base + " --rounds=9").split()))["result"]
+    first = cli.run(parse_argv((base + " --rounds=7 --checkpoint-every=3").split()))
+    ck = first["results_dir"] + "approx_acc_1_5_checkpoint.npz"
+    assert os.path.exists(ck) and int(np.load(ck)["next_round"]) == 6
+    rest = cli.run(parse_argv((base + f" --rounds=9 --resume={ck}").split()))["result"]
+    assert rest.betaset.shape[0] == 3
+    assert np.allclose(rest.betaset, full.betaset[6:], atol=1e-12)
+    with pytest.raises(ValueError):
+        parse_argv((base + " --resume").split())
