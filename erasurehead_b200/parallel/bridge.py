@@ -20,6 +20,10 @@ a slow or dead node delays only its own transfers, and the decoder's stop rule s
 exactly as it skips a straggler inside the node.  Receives go to per-remote streams on the root so
 that the root's own gradient kernels and the decoder never wait for them in stream order.
 
+On the root the receives and arrival kernels of a round are enqueued before that round's decoder kernel:
+the decoder spins on the arrival records, and a kernel issued after a spinning kernel can share its hardware
+queue and never start (the first version, issued the other way round, hung in round 0).
+
 Per pair the operations are issued in one fixed order on both sides (message(s) of round r, then
 the parameters of round r+1), which is what NCCL point-to-point requires.  A remote rank waits for
 the sends of round r-2 before a kernel overwrites those slots again.  The root does not wait for
