@@ -159,3 +159,17 @@ def test_grid_search_deals_points_to_hosts():
         cluster.fan_out = keep
         os.remove(hf)
     assert len(seen) == 2 and "--seed=1" in seen[0] and "--seed=3" in seen[0] and "--seed=2" in seen[1]
+
+
+def test_check_env_script_runs_and_reports():
+    """check_env (role of tools/pre_run.sh): the per-host script is valid shell + Python and names every item;
+    on a machine without a GPU it must fail on the GPU line only where the stack is otherwise complete."""
+    import subprocess
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    p = subprocess.run(["bash", "-c", cluster.CHECK_ENV], capture_output=True, text=True, timeout=120)
+    lines = p.stdout.strip().splitlines()
+    names = [ln.split()[1].rstrip(":") for ln in lines]
+    assert names[:1] == ["python"] and {"torch", "nvcc", "numpy", "scipy"} <= set(names), p.stdout + p.stderr
+    assert all(ln.startswith(("ok   ", "FAIL ")) for ln in lines)
+    assert (p.returncode == 0) == all(ln.startswith("ok") for ln in lines)

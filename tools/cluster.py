@@ -20,6 +20,8 @@ sense for GPU nodes:
                                                `hosts` aliases to /etc/hosts, share one cluster SSH key pair, accept
                                                host keys, so that every node reaches every other by alias
   update_repo <hostfile>                       `git pull` in the repository on every host (tools/update_git_dir.sh role)
+  check_env <hostfile>                         role of tools/pre_run.sh, checked instead of installed: Python, torch + CUDA,
+                                               sm_100 GPUs, NCCL, nvcc, numpy / scipy on every host
   clean_launch_and_run --count N -- main.py <13 positionals>
                                                shutdown, launch, wait until every instance is up and reachable,
                                                get_hosts, bootstrap, install, torchrun (pytorch_ec2.py:938 map entry)
@@ -264,6 +266,47 @@ def cmd_install(a):
     fan_out(read_hosts(a.hostfile), f"cd {repo} && bash csrc/build.sh | tail -1")
 
 
+CHECK_ENV = ("python - <<'PY'\n"
+             "import sys, shutil, subprocess\n"
+             "ok = True\n"
+             "def say(k, v, good=True):\n"
+             "    global ok; ok &= bool(good); print(('ok   ' if good else 'FAIL ') + k + ': ' + str(v))\n"
+             "say('python', sys.version.split()[0], sys.version_info >= (3, 10))\n"
+             "try:\n"
+             "    import torch\n"
+             "    say('torch', torch.__version__ + ' cuda ' + str(torch.version.cuda), torch.cuda.is_available())\n"
+             "    n = torch.cuda.device_count()\n"
+             "    caps = sorted({torch.cuda.get_device_capability(i) for i in range(n)})\n"
+             "    say('gpus', str(n) + ' x ' + (torch.cuda.get_device_name(0) if n else '-') + ' ' + str(caps), n > 0 and caps == [(10, 0)])\n"
+             "    import torch.distributed as d\n"
+             "    say('nccl', '.'.join(map(str, torch.cuda.nccl.version())), d.is_nccl_available())\n"
+             "except Exception as e:\n"
+             "    say('torch', repr(e), False)\n"
+             "nv = shutil.which('nvcc') or '/usr/local/cuda/bin/nvcc'\n"
+             "try:\n"
+             "    out = [l for l in subprocess.run([nv, '--version'], capture_output=True, text=True).stdout.splitlines() if 'release' in l]\n"
+             "    say('nvcc', out[0].strip() if out else 'no version line', bool(out) and ('release 12.' in out[0] or 'release 13.' in out[0]))\n"
+             "except Exception as e:\n"
+             "    say('nvcc', repr(e), False)\n"
+             "for m in ('numpy', 'scipy'):\n"
+             "    try:\n"
+             "        say(m, __import__(m).__version__)\n"
+             "    except Exception as e:\n"
+             "        say(m, repr(e), False)\n"
+             "sys.exit(0 if ok else 1)\n"
+             "PY")
+
+
+def cmd_check_env(a):
+    """What tools/pre_run.sh was for -- a node that can run the code -- checked instead of installed (the
+    software stack is the machine image): Python, torch with CUDA, sm_100 GPUs, NCCL, nvcc, numpy / scipy on every
+    host; a host that fails returns rc 1."""
+    res = fan_out(read_hosts(a.hostfile), CHECK_ENV)
+    bad = [h for h, (rc, _, _) in res.items() if rc != 0]
+    if bad:
+        sys.exit(f"environment check failed on: {' '.join(bad)}")
+
+
 def cmd_bootstrap(a):
     """/etc/hosts aliases + one shared key pair + known_hosts on every node (tools/local_script.sh,
     tools/remote_script.sh).  Reads the `hosts` file written by get_hosts from the current directory."""
@@ -386,7 +429,7 @@ def main(argv=None):
     p = sub.add_parser("get_hosts"); p.add_argument("--hostfile"); p.set_defaults(fn=cmd_get_hosts)
     for name, fn in (("run_command", cmd_run_command), ("list_idle_instances", cmd_list_idle),
                      ("kill_python", cmd_kill_python), ("kill_all_python", cmd_kill_python), ("install", cmd_install),
-                     ("bootstrap", cmd_bootstrap), ("update_repo", cmd_update_repo)):
+                     ("bootstrap", cmd_bootstrap), ("update_repo", cmd_update_repo), ("check_env", cmd_check_env)):
         p = sub.add_parser(name); p.add_argument("hostfile"); p.add_argument("--repo")
         p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=fn)
     p = sub.add_parser("setup_nfs"); p.add_argument("hostfile"); p.add_argument("export_dir"); p.set_defaults(fn=cmd_setup_nfs)
