@@ -1,5 +1,5 @@
-// Native reader for the reference's dense text format (host code only; lives in the CUDA library so
-// that there is one shared object).
+// Native reader and writer for the reference's dense text format (host code only; lives in the CUDA
+// library so that there is one shared object).
 //
 // The reference stores every dense partition as text, one row per line, space-separated decimal
 // floats (util.py:26-30) and reads it back with np.loadtxt (util.py:13-15), which parses a few
@@ -19,7 +19,9 @@
 #include <unistd.h>
 
 #include <atomic>
+#include <charconv>
 #include <chrono>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -285,5 +287,113 @@ extern "C" int eh_load_dense_text(const char* path, int64_t rows, int64_t cols, 
         set_error("load_dense_text: %s: row %lld does not hold exactly %lld numbers", path, bad_row.load() + 1, (long long)cols);
         return EH_EINVAL;
     }
+    return EH_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Writer.  The reference writes a partition with  " ".join(str(x) for x in row)  (util.py:26-30): every value
+// is Python's repr of a double -- the shortest decimal string that reads back to the same double, in positional
+// notation with at least one digit after the point for 1e-4 <= |x| < 1e16 and as d[.ddd]e+XX otherwise.  A
+// million values per second in Python; here std::to_chars supplies the shortest digits and format_repr lays them
+// out by the same rule, rows are formatted by all cores in slabs and written in order, so the file is
+// byte-identical to the reference's.
+// ------------------------------------------------------------------------------------------
+namespace eh {
+
+// Appends repr(v) at p (at least 32 bytes free); returns the new end.
+static inline char* format_repr(char* p, double v) {
+    if (std::isnan(v)) { memcpy(p, "nan", 3); return p + 3; }
+    if (std::isinf(v)) { if (v < 0) *p++ = '-'; memcpy(p, "inf", 3); return p + 3; }
+    char tmp[40];
+    const auto r = std::to_chars(tmp, tmp + sizeof(tmp), v, std::chars_format::scientific);   // [-]d[.ddd]e[+-]XX
+    const char* q = tmp;
+    if (*q == '-') { *p++ = '-'; ++q; }
+    char digits[24];
+    int nd = 0;
+    digits[nd++] = *q++;
+    if (*q == '.') { ++q; while (*q != 'e') digits[nd++] = *q++; }
+    ++q;                                                     // 'e'
+    const bool eneg = (*q == '-');
+    ++q;
+    int ex = 0;
+    while (q < r.ptr) ex = ex * 10 + (*q++ - '0');
+    if (eneg) ex = -ex;
+    if (ex < -4 || ex >= 16) {                               // float_repr_style 'short', format code 'r'
+        *p++ = digits[0];
+        if (nd > 1) { *p++ = '.'; memcpy(p, digits + 1, (size_t)(nd - 1)); p += nd - 1; }
+        *p++ = 'e';
+        *p++ = ex < 0 ? '-' : '+';
+        int a = ex < 0 ? -ex : ex;
+        if (a >= 100) { *p++ = (char)('0' + a / 100); a %= 100; }
+        *p++ = (char)('0' + a / 10);
+        *p++ = (char)('0' + a % 10);
+        return p;
+    }
+    if (ex < 0) {                                            // 0.000ddd
+        *p++ = '0'; *p++ = '.';
+        for (int i = 0; i < -ex - 1; ++i) *p++ = '0';
+        memcpy(p, digits, (size_t)nd);
+        return p + nd;
+    }
+    const int ip = ex + 1;                                   // digits before the point
+    if (nd <= ip) {
+        memcpy(p, digits, (size_t)nd); p += nd;
+        for (int i = nd; i < ip; ++i) *p++ = '0';
+        *p++ = '.'; *p++ = '0';
+        return p;
+    }
+    memcpy(p, digits, (size_t)ip); p += ip;
+    *p++ = '.';
+    memcpy(p, digits + ip, (size_t)(nd - ip));
+    return p + (nd - ip);
+}
+
+}  // namespace eh
+
+extern "C" int eh_format_repr(double v, char* out32) {
+    if (!out32) return EH_EINVAL;
+    char* e = eh::format_repr(out32, v);
+    *e = 0;
+    return (int)(e - out32);
+}
+
+extern "C" int eh_save_dense_text(const char* path, const double* data, int64_t rows, int64_t cols, int64_t ld) {
+    using namespace eh;
+    EH_REQUIRE(path && (data || rows == 0) && rows >= 0 && cols > 0 && ld >= cols, "save_dense_text: bad argument");
+    FILE* f = fopen(path, "wb");
+    EH_REQUIRE(f != nullptr, "save_dense_text: cannot create %s: %s", path, strerror(errno));
+    const unsigned nt = text_threads();
+    // slabs of rows: about 4 MB of text per thread and wave
+    long long slab = (long long)((4u << 20) / (size_t)(cols * 20 + 1));
+    if (slab < 1) slab = 1;
+    std::vector<std::string> buf(nt);
+    bool ok = true;
+    for (long long r0 = 0; r0 < rows && ok; r0 += slab * nt) {
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nt; ++t) {
+            const long long a = r0 + (long long)t * slab, b = std::min<long long>(a + slab, rows);
+            buf[t].clear();
+            if (a >= b) continue;
+            th.emplace_back([&, t, a, b] {
+                std::string& s = buf[t];
+                s.resize((size_t)(b - a) * (size_t)(cols * 26 + 1));
+                char* p = &s[0];
+                for (long long r = a; r < b; ++r) {
+                    const double* row = data + r * ld;
+                    for (long long c = 0; c < cols; ++c) {
+                        if (c) *p++ = ' ';
+                        p = format_repr(p, row[c]);
+                    }
+                    *p++ = '\n';
+                }
+                s.resize((size_t)(p - &s[0]));
+            });
+        }
+        for (auto& x : th) x.join();
+        for (unsigned t = 0; t < nt && ok; ++t)
+            if (!buf[t].empty()) ok = fwrite(buf[t].data(), 1, buf[t].size(), f) == buf[t].size();
+    }
+    const bool closed = fclose(f) == 0;
+    if (!ok || !closed) { set_error("save_dense_text: write to %s failed: %s", path, strerror(errno)); return EH_EINVAL; }
     return EH_OK;
 }

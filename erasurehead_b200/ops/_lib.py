@@ -184,6 +184,8 @@ def _declare(lib):
         "eh_auc_batch_scratch_bytes": (sz, [i64, i32]),
         "eh_text_shape": (i32, [C.c_char_p, P(i64), P(i64)]),
         "eh_load_dense_text": (i32, [C.c_char_p, i64, i64, vp, i64, i32]),
+        "eh_save_dense_text": (i32, [C.c_char_p, vp, i64, i64, i64]),
+        "eh_format_repr": (i32, [C.c_double, C.c_char_p]),
         "eh_synth_gmm": (i32, [vp, vp, i64, i32, i32, u64, u64, i32, i32, vp]),
         "eh_synth_onehot": (i32, [vp, vp, i64, i32, i32, vp, u64, u64, i32, i32, vp]),
         "eh_onehot_assemble": (i32, [vp, vp, i64, i32, vp, vp]),

@@ -50,9 +50,29 @@ def _load_data_native(path: str, dtype=float) -> np.ndarray:
 
 
 def save_matrix(m, path: str) -> None:
+    """One row per line, space-separated ``str(float)`` (util.py:26-30).  Matrices of more than a few thousand
+    values go through the native multi-threaded writer (csrc/textio.cu: shortest round-trip digits laid out by
+    Python's repr rule, byte-identical output, ~100x this loop); small ones, and machines where the library
+    cannot be built, use the loop."""
+    a = np.asarray(m)
+    if a.ndim == 2 and a.size >= (1 << 12) and a.dtype.kind == "f":
+        try:
+            return _save_matrix_native(a, path)
+        except (OSError, ImportError, RuntimeError):
+            pass
     with open(path, "w") as f:
         for row in m:
             f.write(" ".join(repr(float(x)) for x in row) + "\n")
+
+
+def _save_matrix_native(a: np.ndarray, path: str) -> None:
+    from ..ops import _lib
+    L = _lib.lib()
+    if not hasattr(L, "eh_save_dense_text"):
+        raise RuntimeError("native writer not in this build")
+    a = np.ascontiguousarray(a, dtype=np.float64)                 # float(x) of the loop: exact widening of float32
+    _lib.check(L.eh_save_dense_text(path.encode(), a.ctypes.data, a.shape[0], a.shape[1], a.shape[1]),
+               "eh_save_dense_text")
 
 
 def save_vector(v, path: str) -> None:

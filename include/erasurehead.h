@@ -391,6 +391,12 @@ int eh_code_decode_table(const double* d_B, int n, int s, const int32_t* d_missi
  * and columns (numbers on the first line). */
 int eh_text_shape(const char* path, int64_t* rows, int64_t* cols);
 int eh_load_dense_text(const char* path, int64_t rows, int64_t cols, void* h_out, int64_t ld, int elem_bytes);
+/* Native writer of the same format (util.py:26-30: " ".join(str(x)) per row): every value as Python's repr of a
+ * double (shortest round-trip digits; positional for 1e-4 <= |x| < 1e16, else d[.ddd]e+XX), formatted on all cores,
+ * byte-identical to the reference's files.  eh_format_repr writes one value (NUL-terminated, < 32 bytes) and
+ * returns its length. */
+int eh_save_dense_text(const char* path, const double* h_data, int64_t rows, int64_t cols, int64_t ld);
+int eh_format_repr(double v, char* out32);
 
 /* One-hot feature construction (K15): idx[r,c] = offsets[c] + codes[r,c]; pair features as the
  * mixed-radix id of two label-encoded columns (arrange_real_data.py:41-64, util.py:49-55). */

@@ -232,3 +232,39 @@ def test_cli_checkpoint_every_writes_a_resumable_file_on_cpu(tmp_path):
     assert np.allclose(rest.betaset, full.betaset[6:], atol=1e-12)
     with pytest.raises(ValueError):
         parse_argv((base + " --resume").split())
+
+
+def test_native_text_writer_is_byte_identical_to_python_repr(tmp_path):
+    """csrc/textio.cu eh_save_dense_text: the reference's `" ".join(str(x))` rows (util.py:26-30), i.e. Python's
+    repr of every double -- shortest round-trip digits, positional for 1e-4 <= |x| < 1e16, else exponent form."""
+    import ctypes as C
+    try:
+        from erasurehead_b200.ops import _lib
+        L = _lib.lib()
+        L.eh_format_repr
+    except Exception as e:  # noqa: BLE001
+        pytest.skip(f"native library unavailable: {e}")
+    buf = C.create_string_buffer(40)
+
+    def nat(v):
+        n = L.eh_format_repr(float(v), buf)
+        return buf.raw[:n].decode()
+    edge = [0.0, -0.0, 1.0, -1.0, 0.1, 1e-4, 9.999e-5, 1e-5, 1e15, 1e16, 9999999999999998.0, 1.2345e16, 123456.789, 1e22,
+            1e23, 5e-324, 1.7976931348623157e308, 2.2250738585072014e-308, 1e100, 1e-100, 123456789012345.6, 100.0,
+            12345678901234567.0, 2.5e-7, float("inf"), float("-inf"), float("nan"), 1e7, 65536.0, 1 / 3]
+    assert [nat(v) for v in edge] == [repr(v) for v in edge]
+    rng = np.random.RandomState(0)
+    vals = np.frombuffer(rng.bytes(8 * 20000), dtype=np.float64)              # every magnitude and digit count
+    vals = np.concatenate([vals[np.isfinite(vals)], rng.randn(20000), rng.randn(5000) * 1e-6, rng.randn(5000) * 1e18,
+                           rng.randn(5000).astype(np.float32).astype(np.float64)])
+    assert all(nat(v) == repr(float(v)) for v in vals)
+    X = rng.randn(64, 128)
+    X[0, :6] = [1e16, 1e-5, 100.0, -0.0, 123456.0, 5e-324]
+    for M, name in ((X, "d"), (X.astype(np.float32), "f")):
+        p, q = str(tmp_path / f"{name}_native.dat"), str(tmp_path / f"{name}_python.dat")
+        io.save_matrix(M, p)                                                  # >= 4096 values: native path
+        with open(q, "w") as f:
+            for row in M:
+                f.write(" ".join(repr(float(x)) for x in row) + "\n")
+        assert open(p, "rb").read() == open(q, "rb").read()
+        assert np.array_equal(io.load_data(p), M.astype(np.float64))
