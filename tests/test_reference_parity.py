@@ -71,15 +71,17 @@ SEED = 5
 NP_SEED = SEED + 7919          # oracle.initial_beta draws the start from RandomState(seed + 7919)
 
 
-@pytest.mark.parametrize("name,triple,s,k,rule,prefix", [
-    ("naive", ("0", "0", "0"), 0, 0, "GD", "naive_acc"),
-    ("naive", ("0", "0", "0"), 0, 0, "AGD", "naive_acc"),
-    ("coded", ("1", "0", "0"), 1, 0, "AGD", "coded_acc_1"),
-    ("replication", ("1", "0", "1"), 1, 0, "AGD", "replication_acc_1"),
-    ("approx_collect_all", ("1", "0", "3"), 1, 4, "AGD", "replication_acc_1"),       # Q2: AGC writes replication's names
+@pytest.mark.parametrize("name,triple,s,k,rule,prefix,n_procs", [
+    ("naive", ("0", "0", "0"), 0, 0, "GD", "naive_acc", 5),
+    ("naive", ("0", "0", "0"), 0, 0, "AGD", "naive_acc", 5),
+    ("coded", ("1", "0", "0"), 1, 0, "AGD", "coded_acc_1", 5),
+    ("replication", ("1", "0", "1"), 1, 0, "AGD", "replication_acc_1", 5),
+    ("approx_collect_all", ("1", "0", "3"), 1, 4, "AGD", "replication_acc_1", 5),    # Q2: AGC writes replication's names
+    ("coded_s2", ("1", "0", "0"), 2, 0, "GD", "coded_acc_2", 7),                      # 6 workers, any 4 decode
+    ("replication_s2", ("1", "0", "1"), 2, 0, "AGD", "replication_acc_2", 7),        # two groups of three
 ])
-def test_exact_schemes_match_the_reference_files(tmp_path, name, triple, s, k, rule, prefix):
-    n_procs, rows, cols = 5, 8 * 60, 10
+def test_exact_schemes_match_the_reference_files(tmp_path, name, triple, s, k, rule, prefix, n_procs):
+    rows, cols = 8 * 60, 10
     out = generate_gmm_to_disk(n_procs, rows, cols, str(tmp_path), s, 0, 0, seed=3)
     args = [str(n_procs), str(rows), str(cols), str(tmp_path) + "/", "0", "x", triple[0], str(s), triple[1], triple[2],
             str(k), "0", rule]
