@@ -37,9 +37,12 @@ def run_reference(args, timeout=300, np_seed=None):
     return p.stdout
 
 
-@pytest.mark.parametrize("coded_ver,prefix", [(1, "partialreplication_1_3"), (0, "partialcoded_1_3")])
-def test_partial_schemes_match_the_reference_files(tmp_path, coded_ver, prefix):
-    n_procs, rows, cols, s, P = 5, 8 * 60, 10, 1, 3
+@pytest.mark.parametrize("coded_ver,prefix,n_procs,s,P", [
+    (1, "partialreplication_1_3", 5, 1, 3), (0, "partialcoded_1_3", 5, 1, 3),
+    (1, "partialreplication_2_4", 7, 2, 4), (0, "partialcoded_2_4", 7, 2, 4),
+])
+def test_partial_schemes_match_the_reference_files(tmp_path, coded_ver, prefix, n_procs, s, P):
+    rows, cols = 8 * 60, 10
     out = generate_gmm_to_disk(n_procs, rows, cols, str(tmp_path), s, P, 1, seed=3)
     args = [str(n_procs), str(rows), str(cols), str(tmp_path) + "/", "0", "x", "1", str(s), str(P), str(coded_ver),
             "0", "0", "AGD"]
@@ -49,7 +52,7 @@ def test_partial_schemes_match_the_reference_files(tmp_path, coded_ver, prefix):
     ref_files = sorted(os.listdir(ref_dir))
     ref_test = io.load_data(ref_dir + prefix + "_testing_loss.dat")
     ref_auc = io.load_data(ref_dir + prefix + "_auc.dat")
-    tl_prefix = "partialreplication_1_3"            # Q3: partial_coded writes its training loss under this prefix
+    tl_prefix = f"partialreplication_{s}_{P}"       # Q3: partial_coded writes its training loss under this prefix
     ref_train = io.load_data(ref_dir + tl_prefix + "_training_loss.dat")
     for f in ref_files:
         os.rename(ref_dir + f, ref_dir + "ref_" + f)
