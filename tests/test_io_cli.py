@@ -268,3 +268,10 @@ def test_native_text_writer_is_byte_identical_to_python_repr(tmp_path):
                 f.write(" ".join(repr(float(x)) for x in row) + "\n")
         assert open(p, "rb").read() == open(q, "rb").read()
         assert np.array_equal(io.load_data(p), M.astype(np.float64))
+
+
+def test_selfcheck_runs_on_the_cpu_path(capsys):
+    from erasurehead_b200 import selfcheck
+    assert selfcheck.main(["--cpu"]) == 0
+    out = capsys.readouterr().out
+    assert out.count(" ok") == len(selfcheck.CASES) and "all schemes agree" in out

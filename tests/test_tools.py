@@ -121,7 +121,7 @@ def test_torchrun_one_job_over_all_hosts():
     c0 = cluster.torchrun_command(0, 3, "/repo", 8, 29500, ["main.py", "25"], master="10.0.0.1")
     c2 = cluster.torchrun_command(2, 3, "/repo", 8, 29500, ["main.py", "25"], master="10.0.0.1")
     for i, c in ((0, c0), (2, c2)):
-        assert f"--nnodes=3 --node-rank={i} " in c and "--master-addr 10.0.0.1" in c and "EH_NODE_SIZE=8 " in c
+        assert f"--nnodes=3 --node-rank={i} " in c and "--master-addr 10.0.0.1" in c and "setsid env EH_NODE_SIZE=8 python" in c
     seen = []
     cluster_fan_out, cluster.fan_out = cluster.fan_out, lambda hosts, f: seen.extend(f(h) for h in hosts)
     try:
@@ -173,3 +173,24 @@ def test_check_env_script_runs_and_reports():
     assert names[:1] == ["python"] and {"torch", "nvcc", "numpy", "scipy"} <= set(names), p.stdout + p.stderr
     assert all(ln.startswith(("ok   ", "FAIL ")) for ln in lines)
     assert (p.returncode == 0) == all(ln.startswith("ok") for ln in lines)
+
+
+def test_dry_run_prints_commands_and_contacts_nobody(tmp_path, capsys):
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cluster
+    hf = tmp_path / "hosts"
+    hf.write_text("hostA\nhostB\n")
+    keep = cluster.ssh_run
+    cluster.ssh_run = lambda *a, **k: (_ for _ in ()).throw(AssertionError("dry run must not open SSH connections"))
+    try:
+        cluster.main(["--dry-run", "torchrun", "--hostfile", str(hf), "--gpus-per-node", "4", "--one-job", "--", "main.py", "9"])
+        cluster.main(["--dry-run", "check_env", str(hf)])
+    finally:
+        cluster.ssh_run = keep
+        cluster.DRY_RUN = False
+    out = capsys.readouterr().out
+    assert out.count("would run:") == 4 and "[hostB] would run:" in out and "--node-rank=1" in out
+    # the command of a host is valid shell (setsid must be followed by a program, not by an assignment)
+    import subprocess
+    line = [ln for ln in out.splitlines() if "torch.distributed.run" in ln][0].split("would run: ", 1)[1]
+    assert subprocess.run(["bash", "-n", "-c", line]).returncode == 0 and "setsid env " in line

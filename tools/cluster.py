@@ -39,6 +39,8 @@ sense for GPU nodes:
                                                (role of run_mxnet_grid_search / run_mxnet_loss_curve, :374-652: the
                                                per-iteration loss curves are the result files of every run)
 
+``--dry-run`` before the sub-command prints the per-host commands instead of running them.
+
 Unlike the reference, processes are never killed by pattern (``pkill python``): the launcher
 records the PID it started on every host under ``~/.erasurehead_b200/pids`` and only those are
 signalled.  Credentials come from the SSH agent / ``~/.ssh/config``; nothing is hard-coded.
@@ -91,7 +93,16 @@ def ssh_run(host: str, command: str, user: str = None, timeout: int = 600):
         cli.close()
 
 
+DRY_RUN = False          # --dry-run: print what would be run on which host, contact nobody
+
+
 def fan_out(hosts: List[str], command, user=None):
+    if DRY_RUN:
+        res = {}
+        for h in hosts:
+            print(f"[{h}] would run: {command(h) if callable(command) else command}")
+            res[h] = (0, "", "")
+        return res
     with ThreadPoolExecutor(max_workers=min(32, max(1, len(hosts)))) as ex:
         futs = {h: ex.submit(ssh_run, h, command(h) if callable(command) else command, user) for h in hosts}
         res = {}
@@ -355,7 +366,7 @@ def torchrun_command(host_index: int, n_hosts: int, repo: str, gpus_per_node: in
     (erasurehead_b200/parallel/bridge.py); EH_NODE_SIZE tells every rank the layout without a collective."""
     args = " ".join(shlex.quote(x.replace("{node}", str(host_index)).replace("{nodes}", str(n_hosts))) for x in rest)
     if master:
-        rdzv = (f"EH_NODE_SIZE={gpus_per_node} python -m torch.distributed.run --nnodes={n_hosts} --node-rank={host_index} "
+        rdzv = (f"env EH_NODE_SIZE={gpus_per_node} python -m torch.distributed.run --nnodes={n_hosts} --node-rank={host_index} "
                 f"--nproc-per-node={gpus_per_node} --master-addr {master} --master-port {port}")
     else:
         rdzv = (f"python -m torch.distributed.run --nnodes=1 --nproc-per-node={gpus_per_node} "
@@ -420,6 +431,7 @@ def cmd_grid_search(a):
 
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--dry-run", action="store_true", help="print the per-host commands instead of running them over SSH")
     sub = ap.add_subparsers(dest="cmd", required=True)
     p = sub.add_parser("launch"); p.add_argument("--count", type=int, default=cfg["n_workers"])
     p.add_argument("--method", choices=["spot", "ondemand", "reserved"]); p.add_argument("--spot-price")
@@ -447,6 +459,8 @@ def main(argv=None):
     p.add_argument("--gpus-per-node", type=int, default=8); p.add_argument("--port", type=int, default=29500)
     p.add_argument("--repo"); p.add_argument("rest", nargs=argparse.REMAINDER); p.set_defaults(fn=cmd_clean_launch_and_run)
     a = ap.parse_args(argv)
+    global DRY_RUN
+    DRY_RUN = bool(a.dry_run)
     if getattr(a, "rest", None) and a.rest and a.rest[0] == "--":
         a.rest = a.rest[1:]
     a.fn(a)
