@@ -21,8 +21,9 @@ exactly as it skips a straggler inside the node.  Receives go to per-remote stre
 that the root's own gradient kernels and the decoder never wait for them in stream order.
 
 On the root the receives and arrival kernels of a round are enqueued before that round's decoder kernel:
-the decoder spins on the arrival records, and a kernel issued after a spinning kernel can share its hardware
-queue and never start (the first version, issued the other way round, hung in round 0).
+the decoder spins on the arrival records, and nothing a spinning kernel waits for should be issued after it
+(the first version, issued the other way round, hung in round 0 -- most likely a kernel queued behind the spinning
+decoder in a shared hardware queue).
 
 Per pair the operations are issued in one fixed order on both sides (message(s) of round r, then
 the parameters of round r+1), which is what NCCL point-to-point requires.  A remote rank waits for
@@ -130,9 +131,9 @@ class NcclBridge:
         """Enqueued BEFORE the kernels of ``round_``.
 
         Root: the receives of this round's remote messages and their arrival records.  They are issued ahead of
-        the decoder kernel of the round on purpose: the decoder spins until the arrival records appear, and CUDA
-        may place two streams in one hardware queue, where a kernel issued after a spinning kernel would never
-        start -- nothing a spinning kernel waits for may be issued behind it.
+        the decoder kernel of the round on purpose: the decoder spins until the arrival records appear, and
+        nothing a spinning kernel waits for may be issued behind it (two streams can share a hardware queue, where
+        the later kernel would never start).
         Remote rank: the sends of round - 2 used the slots this round's kernels overwrite."""
         if self.ctx.is_root:
             torch, dist = self.torch, self.dist
