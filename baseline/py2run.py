@@ -17,6 +17,11 @@ division" the files were written for.  Nothing else is touched: same drivers, sa
 initial parameters (naive / replication / approximate) and its code matrix B from that generator without
 seeding it; with the variable set the run is reproducible, which is what the parity tests compare against.
 The benchmark arm leaves it unset.
+
+``EH_REF_API_SHIMS=1`` restores two library interfaces the reference's ``arrange_real_data.py`` was written
+against and that current pandas / scikit-learn no longer have: ``DataFrame.ix`` (label-based here,
+which is how the script uses it, arrange_real_data.py:38) and ``OneHotEncoder(sparse=...)`` (now
+``sparse_output``, :61,111,175,218).  Like the division pass this changes the environment, not the file.
 """
 import ast
 import builtins
@@ -91,6 +96,25 @@ class _Finder(importlib.abc.MetaPathFinder):
         return None
 
 
+def _install_api_shims():
+    import pandas as pd
+    from sklearn import preprocessing
+    if not hasattr(pd.DataFrame, "ix"):
+        pd.DataFrame.ix = property(lambda self: self.loc)
+    base = preprocessing.OneHotEncoder
+
+    class OneHotEncoder(base):
+        def __init__(self, *, sparse=None, **kw):
+            if sparse is not None:
+                kw.setdefault("sparse_output", bool(sparse))
+            super().__init__(**kw)
+
+        @classmethod
+        def _get_param_names(cls):
+            return base._get_param_names()
+    preprocessing.OneHotEncoder = OneHotEncoder
+
+
 def main():
     if len(sys.argv) < 2:
         print(__doc__)
@@ -100,6 +124,8 @@ def main():
     sys.meta_path.insert(0, _Finder([os.path.join(root, "src"), root]))
     sys.argv = [sys.argv[1]] + sys.argv[2:]
     sys.path.insert(0, root)
+    if os.environ.get("EH_REF_API_SHIMS"):
+        _install_api_shims()
     if os.environ.get("EH_NP_SEED"):
         np.random.seed(int(os.environ["EH_NP_SEED"]))
     with open(script, "rb") as f:
