@@ -80,3 +80,49 @@ def test_util_helpers_under_the_reference_names(tmp_path):
     assert compat.unique_rows(np.array([[1, 2], [1, 2], [0, 5]])).tolist() == [[0, 5], [1, 2]]
     X = compat.interactionTermsAmazon(np.array([[1, 2, 3], [1, 2, 4]]), degree=2)
     assert X.shape[0] == 2 and X.shape[1] >= 1
+
+
+def _reference_util():
+    """The reference's util.py compiled with Python-2 division (baseline/py2run.py), as a namespace."""
+    import sys
+    root = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+    path = next((p for p in (os.path.join(root, "baseline", "_ref", "src", "util.py"), "/root/reference/src/util.py")
+                 if os.path.exists(p)), None)
+    if path is None:
+        pytest.skip("reference tree not available")
+    sys.path.insert(0, os.path.join(root, "baseline"))
+    import py2run
+    ns = {"__name__": "ref_util", "__builtins__": __builtins__}
+    exec(py2run.compile_py2(open(path, "rb").read(), path), ns)
+    return ns
+
+
+def test_helpers_agree_with_the_reference_util_module(tmp_path):
+    """Same inputs through the reference's own util.py functions and through compat's."""
+    ref = _reference_util()
+    rng = np.random.RandomState(0)
+    for n, s in ((4, 1), (6, 2), (7, 3)):
+        B = ref["getB"](n, s)                                              # the reference's own code matrix
+        assert np.allclose(compat.getA(B, n, s), ref["getA"](B, n, s), atol=1e-9)
+        A = compat.getA(B, n, s)
+        for r in range(A.shape[0]):
+            mask = A[r] != 0
+            assert compat.calculate_indexA(mask) == ref["calculate_indexA"](mask) == r
+        Bm = compat.getB(n, s)                                             # ours has the same structure
+        assert np.array_equal(Bm != 0, B != 0) and np.allclose(ref["getA"](Bm, n, s) @ Bm, 1.0)
+    y, p = rng.choice([-1.0, 1.0], 50), rng.randn(50)
+    assert np.isclose(compat.calculate_loss(y, p, 50), ref["calculate_loss"](y, p, 50))
+    assert np.isclose(compat.calculate_mse(y, p, 50), ref["calculate_mse"](y, p, 50))
+    assert compat.compare([1, 0, 1], [1, 1, 0]) == ref["compare"]([1, 0, 1], [1, 1, 0])
+    M, v = rng.randn(70, 64), rng.randn(9)                                  # 4480 values: the native writer's path
+    for name, fn_a, fn_b, obj in (("m", compat.save_matrix, ref["save_matrix"], M), ("v", compat.save_vector, ref["save_vector"], v)):
+        a, b = str(tmp_path / f"{name}_mine.dat"), str(tmp_path / f"{name}_ref.dat")
+        fn_a(obj, a)
+        fn_b(obj, b)
+        assert open(a, "rb").read() == open(b, "rb").read()
+        assert np.allclose(compat.load_data(b), ref["load_data"](a))
+    from scipy.sparse import random as sprandom
+    S = sprandom(20, 30, density=0.2, format="csr", random_state=1)
+    compat.save_sparse_csr(str(tmp_path / "s_mine"), S)
+    ref["save_sparse_csr"](str(tmp_path / "s_ref"), S)
+    assert (ref["load_sparse_csr"](str(tmp_path / "s_mine")) != compat.load_sparse_csr(str(tmp_path / "s_ref"))).nnz == 0
