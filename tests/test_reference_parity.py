@@ -215,3 +215,24 @@ def test_files_written_by_the_reference_generator_are_read_here(tmp_path, partia
     assert set(np.unique(data.y)) <= {-1.0, 1.0} and data.X_test.shape == (int(0.2 * rows), cols)
     ev = cli.run(cfg)["evaluation"]
     assert ev.training_loss[-1] < ev.training_loss[0] and ev.auc[-1] > 0.6
+
+
+@pytest.mark.parametrize("partial,P", [(0, 0), (1, 3)])
+def test_generator_files_are_byte_identical_to_the_reference_generator(tmp_path, partial, P):
+    """generate_data.py draws from numpy's unseeded global generator; seeded by the harness (EH_NP_SEED) with the
+    value this framework's generator is given, both write the same bytes: partitions, labels and test set."""
+    import filecmp
+    ref_src = os.path.join(ROOT, "baseline", "_ref", "src")
+    if not os.path.exists(os.path.join(ref_src, "generate_data.py")):
+        subprocess.check_call(["bash", os.path.join(ROOT, "baseline", "install_ref.sh")], stdout=subprocess.DEVNULL)
+    ref_root, my_root = str(tmp_path / "ref"), str(tmp_path / "mine")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "baseline", "py2run.py"), os.path.join(ref_src, "generate_data.py"),
+                        "5", "480", "10", ref_root, "1", str(P), str(partial)], capture_output=True, text=True, timeout=300,
+                       cwd=ref_src, env=dict(os.environ, EH_NP_SEED="3"))
+    assert p.returncode == 0, (p.stdout + p.stderr)[-2000:]
+    out = generate_gmm_to_disk(5, 480, 10, my_root, 1, P, partial, seed=3)
+    ref_out = out.replace(my_root, ref_root)
+    files = sorted(os.listdir(out))
+    assert files == sorted(os.listdir(ref_out)) and len(files) == (11 if partial else 7)
+    for f in files:
+        assert filecmp.cmp(out + f, ref_out + f, shallow=False), f
