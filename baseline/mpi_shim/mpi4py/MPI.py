@@ -96,7 +96,14 @@ if _SIZE > 1:
     threading.Thread(target=_listen, daemon=True).start()
 
 
+# EH_MPI_LINK_LATENCY_MS=L: a message from rank r to rank 0 spends r * L milliseconds on its link (tests use it to
+# give the master a deterministic arrival order where the reference has no delay model of its own).
+_LINK_MS = float(os.environ.get("EH_MPI_LINK_LATENCY_MS", "0") or 0)
+
+
 def _send(dest, tag, payload):
+    if _LINK_MS > 0 and dest == 0 and _RANK != 0:
+        time.sleep(_RANK * _LINK_MS * 1e-3)
     with _out_lock:
         s = _out.get(dest)
         if s is None:

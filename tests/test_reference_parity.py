@@ -5,8 +5,8 @@ files, and its result files are compared with ours.
 Without injected delays the reference's arrival order is whatever the operating system makes it, so the
 schemes compared are those whose trajectory does not depend on it: the exact ones (naive, cyclic-MDS coded,
 FRC replication, the two partial schemes) and the approximate scheme asked to collect everything (it then stops
-when every group is covered).  avoidstragg sums whichever n - s messages come first and has no deterministic
-counterpart.  Where the reference draws its start from numpy's unseeded global generator (naive, replication,
+when every group is covered).  avoidstragg sums whichever n - s messages come first; its test pins the arrival
+order through the MPI stand-in's link latencies instead.  Where the reference draws its start from numpy's unseeded global generator (naive, replication,
 approximate: naive.py:23, replication.py:31, approximate_coding.py:32) the harness seeds that generator
 (EH_NP_SEED, see py2run.py) with the value our ``--seed`` derives the same draw from."""
 import os
@@ -236,3 +236,33 @@ def test_generator_files_are_byte_identical_to_the_reference_generator(tmp_path,
     assert files == sorted(os.listdir(ref_out)) and len(files) == (11 if partial else 7)
     for f in files:
         assert filecmp.cmp(out + f, ref_out + f, shallow=False), f
+
+
+def test_avoidstragg_matches_the_reference_under_a_fixed_arrival_order(tmp_path):
+    """The reference's avoidstragg driver has no delay model (avoidstragg.py:121-125): which n - s messages come first
+    is left to the operating system.  The MPI stand-in can give every worker's link its own latency
+    (EH_MPI_LINK_LATENCY_MS: rank r's messages to the master take r * L ms), which makes the master collect workers
+    1 .. n - s in every round -- the set this framework's model collects when no delay is injected (ties go to the
+    lower worker id).  With the arrival order pinned, the sum of the first n - s messages and the rescaled step
+    (avoidstragg.py:114) must give the same iterates."""
+    n_procs, rows, cols, s = 5, 8 * 60, 10, 1
+    out = generate_gmm_to_disk(n_procs, rows, cols, str(tmp_path), s, 0, 0, seed=3)
+    args = [str(n_procs), str(rows), str(cols), str(tmp_path) + "/", "0", "x", "1", str(s), "0", "2", "0", "0", "AGD"]
+    cmd = [sys.executable, os.path.join(ROOT, "baseline", "mpirun_shim.py"), "-np", args[0], "main.py"] + args
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, EH_MPI_LINK_LATENCY_MS="4"))
+    assert p.returncode == 0 and "Iteration 99: Train Loss" in p.stdout, (p.stdout + p.stderr)[-2000:]
+    ref_dir = out + "results/"
+    ref_files = sorted(f for f in os.listdir(ref_dir) if f.endswith(".dat"))
+    prefix = [f for f in ref_files if f.endswith("_training_loss.dat")][0][:-len("_training_loss.dat")]
+    ref = {q: io.load_data(ref_dir + f"{prefix}_{q}.dat") for q in ("training_loss", "testing_loss", "auc", "worker_timeset")}
+    assert np.all(ref["worker_timeset"][:, :3] >= 0) and np.all(ref["worker_timeset"][:, 3] == -1)    # workers 1..3 every round
+    for f in ref_files:
+        os.rename(ref_dir + f, ref_dir + "ref_" + f)
+    ours = cli.run(parse_argv(args + ["--gpus=-1", "--compat", "--quiet", f"--seed={SEED}"]))
+    ev = ours["evaluation"]
+    assert np.array_equal(ours["result"].worker_timeset >= 0, ref["worker_timeset"] >= 0)
+    assert np.abs(ev.training_loss - ref["training_loss"]).max() <= 1.5e-3
+    assert np.abs(ev.testing_loss - ref["testing_loss"]).max() <= 1.5e-3
+    assert np.abs(ev.auc - ref["auc"]).max() <= 1.5e-3
+    mine = sorted(f for f in os.listdir(ref_dir) if f.endswith(".dat") and not f.startswith("ref_"))
+    assert mine == ref_files
